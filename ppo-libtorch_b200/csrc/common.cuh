@@ -1,0 +1,105 @@
+// common.cuh — shared helpers for the sm_100a PPO kernels: error plumbing for the C ABI,
+// Philox4x32-10, the flat parameter-slab layout (reference order, PPO/Agent.cpp:41-66).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+
+#include "../../include/ppo_b200.h"
+
+namespace ppo {
+
+// ---------------------------------------------------------------- error plumbing
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define PPO_CUDA(call)                                                        \
+    do {                                                                      \
+        cudaError_t _e = (call);                                              \
+        if (_e != cudaSuccess) return ::ppo::cuda_fail(_e, #call, __FILE__, __LINE__); \
+    } while (0)
+#define PPO_LAUNCH_CHECK() PPO_CUDA(cudaGetLastError())
+#define PPO_REQUIRE(cond, ...)                  \
+    do {                                        \
+        if (!(cond)) {                          \
+            ::ppo::set_error(__VA_ARGS__);      \
+            return PPO_ERR_ARG;                 \
+        }                                       \
+    } while (0)
+
+int sm_count();  // cached multiprocessor count of the current device (0 if no device)
+
+// ---------------------------------------------------------------- dims helpers
+struct Dims {
+    int O, H, heads, K;  // K = total logits
+    int nvec[PPO_MAX_HEADS];
+};
+int make_dims(const ppo_dims* d, Dims* out);  // validates; PPO_OK or PPO_ERR_ARG
+
+// Offsets (in floats) into the flat slab; critic first (PPO/Agent.cpp:41-47), then actor (:52-66).
+struct NetOff {
+    int W1, b1, W2, b2, W3, b3;
+};
+__host__ __device__ inline NetOff critic_off(int O, int H) {
+    NetOff n;
+    n.W1 = 0;
+    n.b1 = n.W1 + H * O;
+    n.W2 = n.b1 + H;
+    n.b2 = n.W2 + H * H;
+    n.W3 = n.b2 + H;
+    n.b3 = n.W3 + H;
+    return n;
+}
+__host__ __device__ inline int critic_size(int O, int H) { return H * O + H + H * H + H + H + 1; }
+__host__ __device__ inline NetOff actor_off(int O, int H, int K) {
+    const int base = critic_size(O, H);
+    NetOff n;
+    n.W1 = base;
+    n.b1 = n.W1 + H * O;
+    n.W2 = n.b1 + H;
+    n.b2 = n.W2 + H * H;
+    n.W3 = n.b2 + H;
+    n.b3 = n.W3 + K * H;
+    return n;
+}
+__host__ __device__ inline int num_params(int O, int H, int K) {
+    return critic_size(O, H) + H * O + H + H * H + H + K * H + K;
+}
+
+// ---------------------------------------------------------------- Philox4x32-10
+// Counter-based RNG (Salmon et al. 2011).  key = 64-bit seed, counter = (c0,c1,c2,c3).
+struct Philox {
+    static constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+    static constexpr uint32_t W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+    __host__ __device__ static inline void round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+#ifdef __CUDA_ARCH__
+        const uint32_t hi0 = __umulhi(M0, c[0]), hi1 = __umulhi(M1, c[2]);
+#else
+        const uint32_t hi0 = (uint32_t)(((uint64_t)M0 * c[0]) >> 32);
+        const uint32_t hi1 = (uint32_t)(((uint64_t)M1 * c[2]) >> 32);
+#endif
+        const uint32_t lo0 = M0 * c[0], lo1 = M1 * c[2];
+        const uint32_t n0 = hi1 ^ c[1] ^ k0, n1 = lo1, n2 = hi0 ^ c[3] ^ k1, n3 = lo0;
+        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+    }
+    // 4 x 32 random bits for (seed, a, b, c, d)
+    __host__ __device__ static inline void gen(uint64_t seed, uint32_t a, uint32_t b, uint32_t c_, uint32_t d,
+                                               uint32_t (&out)[4]) {
+        uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+        out[0] = a; out[1] = b; out[2] = c_; out[3] = d;
+#pragma unroll
+        for (int r = 0; r < 10; r++) {
+            round(out, k0, k1);
+            k0 += W0; k1 += W1;
+        }
+    }
+    // canonical uniform in [0,1): top 24 bits
+    __host__ __device__ static inline float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+};
+// stream ids so that resets, sampling and permutations never share a counter
+enum { RNG_STREAM_RESET = 1, RNG_STREAM_SAMPLE = 2 };
+
+static inline cudaStream_t as_stream(ppo_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+}  // namespace ppo

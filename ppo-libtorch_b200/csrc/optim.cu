@@ -1,0 +1,283 @@
+// optim.cu — K6 and the small reductions around the update:
+//   ppo_clip_adamw          clip_grad_norm_ + AdamW in one launch   (PPO/PPO_Discrete.cpp:640-641)
+//   ppo_adv_stats(_finalize) per-minibatch advantage mean / unbiased std (:591-594)
+//   ppo_explained_variance  1 - var(R - V)/var(R)                   (:647-648)
+//   ppo_make_permutation    counter-based replacement of torch::randperm (:569)
+#include "common.cuh"
+
+namespace ppo {
+
+// ------------------------------------------------------------------------------------------------
+// block-wide sum of doubles in a fixed order (deterministic); result valid in every thread
+template <int THREADS>
+__device__ inline double block_sum(double v, double* sh /* [THREADS/32] */) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < THREADS / 32; w++) t += sh[w];
+    return t;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K6.  Every CTA recomputes the full gradient norm in the same order (P <= 134k floats, L2-resident),
+// so all CTAs agree bit-for-bit on the clip coefficient without a grid barrier; each then applies
+// clip + decoupled weight decay + Adam to its own slice.  `grads` is read-only here (other CTAs are
+// still reading it for their norm), so unlike clip_grad_norm_ the stored gradient stays PRE-clip.
+//   torch/nn/utils/clip_grad.h: coef = max_norm / (norm + 1e-6), applied iff < 1
+//   torch/csrc/api/src/optim/adamw.cpp: p *= 1 - lr*wd; m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2;
+//                                       p -= lr/bc1 * m / (sqrt(v)/sqrt(bc2) + eps)
+constexpr int ADAM_THREADS = 512;
+__global__ void __launch_bounds__(ADAM_THREADS) clip_adamw_kernel(
+    float* __restrict__ params, const float* __restrict__ grads, float* __restrict__ m, float* __restrict__ v, int64_t n,
+    float lr_host, const float* __restrict__ d_lr, float beta1, float beta2, float eps, float weight_decay,
+    int64_t step_host, const int64_t* __restrict__ d_step, float max_grad_norm, float grad_scale,
+    float* __restrict__ norm_out, const float* __restrict__ diag_src, float* __restrict__ diag_dst) {
+    __shared__ double sh[ADAM_THREADS / 32];
+    if (diag_dst && blockIdx.x == 0 && threadIdx.x < 8) diag_dst[threadIdx.x] = diag_src[threadIdx.x];
+    double ss = 0.0;
+    for (int64_t i = threadIdx.x; i < n; i += ADAM_THREADS) {
+        const float gsc = grads[i] * grad_scale;
+        ss += (double)gsc * (double)gsc;
+    }
+    const double norm = sqrt(block_sum<ADAM_THREADS>(ss, sh));
+    if (norm_out && blockIdx.x == 0 && threadIdx.x == 0) *norm_out = (float)norm;
+    const double coef = (double)max_grad_norm / (norm + 1e-6);
+    const float cf = (max_grad_norm > 0.0f && coef < 1.0) ? (float)coef : 1.0f;
+
+    const float lr = d_lr ? *d_lr : lr_host;
+    const int64_t step = step_host + (d_step ? *d_step : 0);
+    const double b1 = (double)beta1, b2 = (double)beta2;
+    const double bc1 = 1.0 - pow(b1, (double)step);
+    const double bc2 = 1.0 - pow(b2, (double)step);
+    const float decay = (float)(1.0 - (double)lr * (double)weight_decay);
+    const float omb1 = (float)(1.0 - b1), omb2 = (float)(1.0 - b2);
+    const float sq_bc2 = (float)sqrt(bc2);
+    const float neg_step = (float)(-((double)lr / bc1));
+    for (int64_t i = (int64_t)blockIdx.x * ADAM_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * ADAM_THREADS) {
+        float g = __fmul_rn(grads[i], grad_scale);
+        if (cf != 1.0f) g = __fmul_rn(g, cf);
+        const float p = __fmul_rn(params[i], decay);
+        const float mi = __fadd_rn(__fmul_rn(m[i], beta1), __fmul_rn(g, omb1));
+        const float vi = __fadd_rn(__fmul_rn(v[i], beta2), __fmul_rn(__fmul_rn(g, g), omb2));
+        m[i] = mi;
+        v[i] = vi;
+        const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(vi), sq_bc2), eps);
+        params[i] = __fadd_rn(p, __fmul_rn(neg_step, __fdiv_rn(mi, denom)));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// advantage statistics: one CTA per minibatch, two passes in double like LibTorch's mean()/std()
+constexpr int STAT_THREADS = 1024;
+__global__ void __launch_bounds__(STAT_THREADS) adv_stats_kernel(const float* __restrict__ adv,
+                                                                 const int32_t* __restrict__ perm, int64_t batch,
+                                                                 int mb_size, float* __restrict__ stats_out,
+                                                                 double* __restrict__ partial_out) {
+    __shared__ double sh[STAT_THREADS / 32];
+    const int mb = blockIdx.x;
+    const int64_t start = (int64_t)mb * mb_size;
+    int64_t cnt = batch - start;
+    if (cnt > mb_size) cnt = mb_size;
+    if (cnt < 0) cnt = 0;
+    double s = 0.0;
+    for (int64_t i = threadIdx.x; i < cnt; i += STAT_THREADS) {
+        const int64_t r = perm ? (int64_t)perm[start + i] : start + i;
+        s += (double)__ldg(adv + r);
+    }
+    const double sum = block_sum<STAT_THREADS>(s, sh);
+    const double mean = cnt > 0 ? sum / (double)cnt : 0.0;
+    if (partial_out) {
+        // raw moments for the data-parallel merge
+        double q = 0.0;
+        for (int64_t i = threadIdx.x; i < cnt; i += STAT_THREADS) {
+            const int64_t r = perm ? (int64_t)perm[start + i] : start + i;
+            const double x = (double)__ldg(adv + r);
+            q += x * x;
+        }
+        const double sq = block_sum<STAT_THREADS>(q, sh);
+        if (threadIdx.x == 0) {
+            partial_out[mb * 3 + 0] = (double)cnt;
+            partial_out[mb * 3 + 1] = sum;
+            partial_out[mb * 3 + 2] = sq;
+        }
+    }
+    if (stats_out) {
+        double q = 0.0;
+        for (int64_t i = threadIdx.x; i < cnt; i += STAT_THREADS) {
+            const int64_t r = perm ? (int64_t)perm[start + i] : start + i;
+            const double dlt = (double)__ldg(adv + r) - mean;
+            q += dlt * dlt;
+        }
+        const double ssd = block_sum<STAT_THREADS>(q, sh);
+        if (threadIdx.x == 0) {
+            stats_out[mb * 2 + 0] = (float)mean;
+            stats_out[mb * 2 + 1] = (float)sqrt(ssd / (double)(cnt - 1));
+        }
+    }
+}
+
+__global__ void adv_stats_finalize_kernel(const double* __restrict__ partial, int n_mb, float* __restrict__ stats_out) {
+    const int mb = blockIdx.x * blockDim.x + threadIdx.x;
+    if (mb >= n_mb) return;
+    const double n = partial[mb * 3 + 0], s = partial[mb * 3 + 1], q = partial[mb * 3 + 2];
+    const double mean = s / n;
+    double var = (q - n * mean * mean) / (n - 1.0);
+    if (var < 0.0) var = 0.0;
+    stats_out[mb * 2 + 0] = (float)mean;
+    stats_out[mb * 2 + 1] = (float)sqrt(var);
+}
+
+// ------------------------------------------------------------------------------------------------
+// explained variance: grid-wide raw moments in double, finished by the last CTA to arrive.
+// workspace: 4*EV_MAX_BLOCKS doubles + one uint32 ticket, zero-initialised; left zeroed on exit.
+constexpr int EV_THREADS = 256;
+constexpr int EV_MAX_BLOCKS = 1024;
+__global__ void __launch_bounds__(EV_THREADS) explained_variance_kernel(int64_t n, const float* __restrict__ ret,
+                                                                        const float* __restrict__ val,
+                                                                        double* __restrict__ part,
+                                                                        unsigned int* __restrict__ ticket,
+                                                                        float* __restrict__ out) {
+    __shared__ double sh[EV_THREADS / 32];
+    __shared__ bool last;
+    double sr = 0, srr = 0, sd = 0, sdd = 0;
+    for (int64_t i = (int64_t)blockIdx.x * EV_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * EV_THREADS) {
+        const float r = __ldg(ret + i);
+        const double rr = (double)r, d = (double)(r - __ldg(val + i));
+        sr += rr; srr += rr * rr; sd += d; sdd += d * d;
+    }
+    sr = block_sum<EV_THREADS>(sr, sh);
+    srr = block_sum<EV_THREADS>(srr, sh);
+    sd = block_sum<EV_THREADS>(sd, sh);
+    sdd = block_sum<EV_THREADS>(sdd, sh);
+    if (threadIdx.x == 0) {
+        part[blockIdx.x * 4 + 0] = sr; part[blockIdx.x * 4 + 1] = srr;
+        part[blockIdx.x * 4 + 2] = sd; part[blockIdx.x * 4 + 3] = sdd;
+        __threadfence();
+        last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    double a[4] = {0, 0, 0, 0};
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += EV_THREADS)
+#pragma unroll
+        for (int k = 0; k < 4; k++) a[k] += part[b * 4 + k];
+#pragma unroll
+    for (int k = 0; k < 4; k++) a[k] = block_sum<EV_THREADS>(a[k], sh);
+    if (threadIdx.x == 0) {
+        const double N = (double)n;
+        const double vr = (a[1] - a[0] * a[0] / N) / (N - 1.0);
+        const double vd = (a[3] - a[2] * a[2] / N) / (N - 1.0);
+        *out = (float)(1.0 - vd / vr);
+        *ticket = 0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Permutation of [0, batch): a 4-round Feistel network on the smallest even-width bit domain that
+// covers `batch`, with cycle walking back into range (a bijection for every batch size).
+__device__ inline uint32_t feistel(uint32_t x, int half_bits, const uint32_t (&k)[4]) {
+    const uint32_t hm = (1u << half_bits) - 1u;
+    uint32_t l = x >> half_bits, r = x & hm;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        uint32_t f = (r ^ k[i]) * 0x9E3779B1u;
+        f ^= f >> 15; f *= 0x85EBCA77u; f ^= f >> 13;
+        const uint32_t nl = r, nr = l ^ (f & hm);
+        l = nl; r = nr;
+    }
+    return (l << half_bits) | r;
+}
+__global__ void __launch_bounds__(256) permutation_kernel(int64_t batch, int half_bits, uint64_t seed, uint64_t epoch,
+                                                          const uint64_t* __restrict__ d_epoch,
+                                                          int32_t* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= batch) return;
+    if (d_epoch) epoch += *d_epoch;
+    uint32_t r[4];
+    Philox::gen(seed, 0x7065726Du /* 'perm' */, 3u, (uint32_t)epoch, (uint32_t)(epoch >> 32), r);
+    uint32_t x = (uint32_t)i;
+    do { x = feistel(x, half_bits, r); } while ((int64_t)x >= batch);
+    out[i] = (int32_t)x;
+}
+
+}  // namespace ppo
+
+using namespace ppo;
+
+namespace ppo {
+int clip_adamw_launch(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_params, float lr,
+                      const float* d_lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                      const int64_t* d_step, float max_grad_norm, float grad_scale, float* norm_out,
+                      const float* diag_src, float* diag_dst, cudaStream_t st) {
+    PPO_REQUIRE(params && grads && exp_avg && exp_avg_sq && n_params >= 0, "ppo_clip_adamw: null buffer");
+    if (n_params == 0) return PPO_OK;
+    int blocks = (int)((n_params + ADAM_THREADS * 4 - 1) / (ADAM_THREADS * 4));
+    if (blocks > 64) blocks = 64;
+    clip_adamw_kernel<<<blocks, ADAM_THREADS, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n_params, lr, d_lr, beta1,
+                                                       beta2, eps, weight_decay, step, d_step, max_grad_norm,
+                                                       grad_scale, norm_out, diag_src, diag_dst);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+}  // namespace ppo
+
+extern "C" int ppo_clip_adamw(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_params,
+                              float lr, const float* d_lr, float beta1, float beta2, float eps, float weight_decay,
+                              int64_t step, const int64_t* d_step, float max_grad_norm, float grad_scale,
+                              float* norm_out, ppo_stream_t stream) {
+    return clip_adamw_launch(params, grads, exp_avg, exp_avg_sq, n_params, lr, d_lr, beta1, beta2, eps, weight_decay,
+                             step, d_step, max_grad_norm, grad_scale, norm_out, nullptr, nullptr, as_stream(stream));
+}
+
+extern "C" int ppo_adv_stats(const float* adv, const int32_t* perm, int64_t batch, int mb_size, int n_mb,
+                             float* stats_out, double* partial_out, ppo_stream_t stream) {
+    PPO_REQUIRE(adv && mb_size >= 1 && n_mb >= 0 && batch >= 0, "ppo_adv_stats: bad arguments");
+    PPO_REQUIRE(stats_out || partial_out, "ppo_adv_stats: no output requested");
+    if (n_mb == 0) return PPO_OK;
+    adv_stats_kernel<<<n_mb, STAT_THREADS, 0, as_stream(stream)>>>(adv, perm, batch, mb_size, stats_out, partial_out);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
+extern "C" int ppo_adv_stats_finalize(const double* partial, int n_mb, float* stats_out, ppo_stream_t stream) {
+    PPO_REQUIRE(partial && stats_out && n_mb >= 0, "ppo_adv_stats_finalize: bad arguments");
+    if (n_mb == 0) return PPO_OK;
+    adv_stats_finalize_kernel<<<(n_mb + 63) / 64, 64, 0, as_stream(stream)>>>(partial, n_mb, stats_out);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
+extern "C" int64_t ppo_explained_variance_workspace_bytes(void) {
+    return (int64_t)EV_MAX_BLOCKS * 4 * sizeof(double) + 16;
+}
+
+extern "C" int ppo_explained_variance(int64_t n, const float* returns, const float* values, void* workspace,
+                                      float* out, ppo_stream_t stream) {
+    PPO_REQUIRE(n >= 2 && returns && values && workspace && out, "ppo_explained_variance: bad arguments");
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    int64_t blocks = (n + EV_THREADS * 8 - 1) / (EV_THREADS * 8);
+    if (blocks > 4 * sms) blocks = 4 * sms;
+    if (blocks > EV_MAX_BLOCKS) blocks = EV_MAX_BLOCKS;
+    double* part = reinterpret_cast<double*>(workspace);
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(part + (size_t)EV_MAX_BLOCKS * 4);
+    explained_variance_kernel<<<(int)blocks, EV_THREADS, 0, as_stream(stream)>>>(n, returns, values, part, ticket, out);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
+extern "C" int ppo_make_permutation(int64_t batch, uint64_t seed, uint64_t epoch, const uint64_t* d_epoch,
+                                    int32_t* perm_out, ppo_stream_t stream) {
+    PPO_REQUIRE(batch >= 0 && batch <= 0x7fffffffLL && (perm_out || batch == 0), "ppo_make_permutation: bad arguments");
+    if (batch == 0) return PPO_OK;
+    int bits = 2;
+    while (bits < 32 && (1ll << bits) < batch) bits += 2;
+    const int64_t blocks = (batch + 255) / 256;
+    permutation_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(batch, bits / 2, seed, epoch, d_epoch, perm_out);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}

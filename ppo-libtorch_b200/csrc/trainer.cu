@@ -1,0 +1,416 @@
+// trainer.cu — host side of one PPO iteration: the body of PPO_Discrete::train /
+// PPO_MultiDiscrete::train (PPO/PPO_Discrete.cpp:511-673 minus printing and checkpointing) as a
+// stream of kernel launches over one device arena, with no host round trip inside an iteration.
+//
+//   rollout (1 launch) -> GAE (1) -> per epoch { permutation (1), advantage statistics (1),
+//   per minibatch { fused fwd+loss+bwd (2), [gradient allreduce], clip + AdamW (1) } }
+//   -> explained variance (1) -> one D2H of the diagnostics.
+//
+// With use_cuda_graph the whole iteration is captured once and replayed; the values that change
+// between iterations (learning rate, optimiser step, RNG counters) live in device scalars.
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace ppo {
+int clip_adamw_launch(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_params, float lr,
+                      const float* d_lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                      const int64_t* d_step, float max_grad_norm, float grad_scale, float* norm_out,
+                      const float* diag_src, float* diag_dst, cudaStream_t st);
+}
+struct ppo_comm;
+extern "C" int ppo_comm_allreduce_f32(ppo_comm* c, float* buf, int64_t count, ppo_stream_t stream);
+extern "C" int ppo_comm_allreduce_f64(ppo_comm* c, double* buf, int64_t count, ppo_stream_t stream);
+extern "C" int ppo_comm_world_size(const ppo_comm* c);
+
+using namespace ppo;
+
+namespace {
+struct Scalars {           // device scalars a captured graph reads
+    uint64_t rollout_counter;  // Philox counter base of this rollout
+    uint64_t epoch_counter;    // permutation epoch base of this update
+    int64_t step_base;         // optimiser steps taken before this iteration
+    float lr;
+    float pad;
+};
+struct Readback {          // one D2H per iteration
+    float ev, grad_norm;
+    double ep_stats[3];
+};
+}  // namespace
+
+struct ppo_trainer {
+    ppo_trainer_cfg cfg;
+    Dims d;
+    int P = 0;
+    int64_t B = 0;
+    int mb_size = 0, n_mb = 0, n_opt = 0;  // n_opt = optimiser steps per iteration
+    char* arena = nullptr;
+    size_t arena_bytes = 0;
+    std::map<std::string, std::pair<void*, int64_t>> buf;
+    // device
+    float *params, *grads, *exp_avg, *exp_avg_sq;
+    float *state, *ep_ret, *next_done, *next_value;
+    int32_t* ep_len;
+    float *obs, *logprobs, *rewards, *dones, *values, *adv, *ret;
+    int32_t *actions, *perm;
+    uint8_t* masks;
+    float *adv_stats, *diag_hist, *ev_out, *norm_out;
+    double *adv_partial, *ep_stats;
+    void *upd_ws, *ev_ws;
+    Scalars* d_scal;
+    // host
+    float* h_diag = nullptr;    // pinned [n_opt, 8]
+    Readback* h_rb = nullptr;   // pinned
+    int64_t step = 0;
+    uint64_t rollout_counter = 0, epoch_counter = 0;
+    ppo_comm* comm = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    cudaStream_t graph_stream = nullptr;
+    int opt_in_iter = 0;  // optimiser steps issued in the current iteration (split-phase API)
+};
+
+static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+extern "C" void ppo_trainer_destroy(ppo_trainer* t) {
+    if (!t) return;
+    if (t->graph_exec) cudaGraphExecDestroy(t->graph_exec);
+    if (t->arena) cudaFree(t->arena);
+    if (t->h_diag) cudaFreeHost(t->h_diag);
+    if (t->h_rb) cudaFreeHost(t->h_rb);
+    delete t;
+}
+
+extern "C" ppo_trainer* ppo_trainer_create(const ppo_trainer_cfg* c) {
+    if (!c) { set_error("ppo_trainer_create: null cfg"); return nullptr; }
+    if (ppo_device_count() <= 0) {
+        set_error("ppo_trainer_create: no CUDA device (there is no CPU fallback)");
+        return nullptr;
+    }
+    ppo_trainer* t = new ppo_trainer();
+    t->cfg = *c;
+    if (make_dims(&c->dims, &t->d)) { delete t; return nullptr; }
+    const int S = ppo_env_state_dim(c->env_kind);
+    if (S < 0 || S != t->d.O) {
+        set_error("ppo_trainer_create: env kind %d observes %d floats but obs_dim=%d", c->env_kind, S, t->d.O);
+        delete t;
+        return nullptr;
+    }
+    if (c->num_envs < 1 || c->num_steps < 1 || c->num_minibatches < 1 || c->update_epochs < 0) {
+        set_error("ppo_trainer_create: bad sizes");
+        delete t;
+        return nullptr;
+    }
+    t->P = num_params(t->d.O, t->d.H, t->d.K);
+    t->B = (int64_t)c->num_envs * c->num_steps;
+    t->mb_size = (int)(t->B / c->num_minibatches);  // PPO_Discrete.cpp:246-247 (integer division)
+    if (t->mb_size < 1) { set_error("ppo_trainer_create: minibatch size 0"); delete t; return nullptr; }
+    t->n_mb = (int)((t->B + t->mb_size - 1) / t->mb_size);  // :573 loop count (last slice may be short)
+    t->n_opt = t->n_mb * c->update_epochs;
+    const bool masked = c->masked != 0;
+
+    struct Item { const char* name; void** ptr; size_t bytes; };
+    const int N = c->num_envs, T = c->num_steps, O = t->d.O, K = t->d.K, heads = t->d.heads;
+    const size_t P = (size_t)t->P;
+    std::vector<Item> items = {
+        {"params", (void**)&t->params, P * 4},
+        {"grads", (void**)&t->grads, (P + 8) * 4},  // + 8 diagnostics in the tail (one allreduce)
+        {"exp_avg", (void**)&t->exp_avg, P * 4},
+        {"exp_avg_sq", (void**)&t->exp_avg_sq, P * 4},
+        {"state", (void**)&t->state, (size_t)S * N * 4},
+        {"ep_len", (void**)&t->ep_len, (size_t)N * 4},
+        {"ep_ret", (void**)&t->ep_ret, (size_t)N * 4},
+        {"next_done", (void**)&t->next_done, (size_t)N * 4},
+        {"next_value", (void**)&t->next_value, (size_t)N * 4},
+        {"obs", (void**)&t->obs, (size_t)T * N * O * 4},
+        {"actions", (void**)&t->actions, (size_t)T * N * heads * 4},
+        {"logprobs", (void**)&t->logprobs, (size_t)T * N * 4},
+        {"rewards", (void**)&t->rewards, (size_t)T * N * 4},
+        {"dones", (void**)&t->dones, (size_t)T * N * 4},
+        {"values", (void**)&t->values, (size_t)T * N * 4},
+        {"adv", (void**)&t->adv, (size_t)T * N * 4},
+        {"ret", (void**)&t->ret, (size_t)T * N * 4},
+        {"masks", (void**)&t->masks, masked ? (size_t)T * N * K : 0},
+        {"perm", (void**)&t->perm, (size_t)t->B * 4},
+        {"adv_stats", (void**)&t->adv_stats, (size_t)t->n_mb * 2 * 4},
+        {"adv_partial", (void**)&t->adv_partial, (size_t)t->n_mb * 3 * 8},
+        {"diag", (void**)&t->diag_hist, (size_t)(t->n_opt > 0 ? t->n_opt : 1) * 8 * 4},
+        {"ev_out", (void**)&t->ev_out, 4},
+        {"norm_out", (void**)&t->norm_out, 4},
+        {"ep_stats", (void**)&t->ep_stats, 3 * 8},
+        {"scalars", (void**)&t->d_scal, sizeof(Scalars)},
+        {"upd_ws", (void**)&t->upd_ws, (size_t)ppo_update_workspace_bytes(&c->dims)},
+        {"ev_ws", (void**)&t->ev_ws, (size_t)ppo_explained_variance_workspace_bytes()},
+    };
+    size_t total = 0;
+    for (auto& it : items) total += al256(it.bytes);
+    if (cudaMalloc(&t->arena, total) != cudaSuccess) {
+        set_error("ppo_trainer_create: cudaMalloc(%zu B) failed: %s", total, cudaGetErrorString(cudaGetLastError()));
+        t->arena = nullptr;
+        ppo_trainer_destroy(t);
+        return nullptr;
+    }
+    t->arena_bytes = total;
+    cudaMemset(t->arena, 0, total);
+    size_t off = 0;
+    for (auto& it : items) {
+        *it.ptr = it.bytes ? (void*)(t->arena + off) : nullptr;
+        t->buf[it.name] = {*it.ptr, (int64_t)it.bytes};
+        off += al256(it.bytes);
+    }
+    if (cudaMallocHost(&t->h_diag, (size_t)(t->n_opt > 0 ? t->n_opt : 1) * 8 * 4) != cudaSuccess ||
+        cudaMallocHost(&t->h_rb, sizeof(Readback)) != cudaSuccess) {
+        set_error("ppo_trainer_create: cudaMallocHost failed");
+        ppo_trainer_destroy(t);
+        return nullptr;
+    }
+    cudaDeviceSynchronize();
+    return t;
+}
+
+extern "C" int ppo_trainer_set_comm(ppo_trainer* t, ppo_comm* comm) {
+    PPO_REQUIRE(t, "null trainer");
+    t->comm = comm;
+    if (comm) PPO_REQUIRE(ppo_comm_world_size(comm) == t->cfg.world_size, "comm world size != cfg.world_size");
+    return PPO_OK;
+}
+
+extern "C" void* ppo_trainer_buffer(ppo_trainer* t, const char* name, int64_t* bytes) {
+    if (!t || !name) return nullptr;
+    auto it = t->buf.find(name);
+    if (it == t->buf.end()) { set_error("ppo_trainer_buffer: unknown buffer '%s'", name); return nullptr; }
+    if (bytes) *bytes = it->second.second;
+    return it->second.first;
+}
+
+extern "C" int ppo_trainer_set_params(ppo_trainer* t, const float* h) {
+    PPO_REQUIRE(t && h, "null argument");
+    PPO_CUDA(cudaMemcpy(t->params, h, (size_t)t->P * 4, cudaMemcpyHostToDevice));
+    return PPO_OK;
+}
+extern "C" int ppo_trainer_get_params(ppo_trainer* t, float* h) {
+    PPO_REQUIRE(t && h, "null argument");
+    PPO_CUDA(cudaMemcpy(h, t->params, (size_t)t->P * 4, cudaMemcpyDeviceToHost));
+    return PPO_OK;
+}
+extern "C" int ppo_trainer_get_opt_state(ppo_trainer* t, float* m, float* v, int64_t* step) {
+    PPO_REQUIRE(t, "null trainer");
+    if (m) PPO_CUDA(cudaMemcpy(m, t->exp_avg, (size_t)t->P * 4, cudaMemcpyDeviceToHost));
+    if (v) PPO_CUDA(cudaMemcpy(v, t->exp_avg_sq, (size_t)t->P * 4, cudaMemcpyDeviceToHost));
+    if (step) *step = t->step;
+    return PPO_OK;
+}
+extern "C" int ppo_trainer_set_opt_state(ppo_trainer* t, const float* m, const float* v, int64_t step) {
+    PPO_REQUIRE(t && step >= 0, "bad argument");
+    if (m) PPO_CUDA(cudaMemcpy(t->exp_avg, m, (size_t)t->P * 4, cudaMemcpyHostToDevice));
+    if (v) PPO_CUDA(cudaMemcpy(t->exp_avg_sq, v, (size_t)t->P * 4, cudaMemcpyHostToDevice));
+    t->step = step;
+    return PPO_OK;
+}
+
+// initEnvs (PPO_Discrete.cpp:365-402): reset every env; next_done = 0 (:502)
+extern "C" int ppo_trainer_reset_envs(ppo_trainer* t) {
+    PPO_REQUIRE(t, "null trainer");
+    const int N = t->cfg.num_envs;
+    // env RNG key = global env index; ppo_env_reset keys on the local index, so offset the seed stream
+    // through the counter: use the dedicated init counter ~0 and a rank-salted seed.
+    int rc = ppo_env_reset(t->cfg.env_kind, N, t->state, t->ep_len, t->ep_ret, nullptr,
+                           t->cfg.seed + 0x9E3779B97F4A7C15ull * (uint64_t)(t->cfg.rank + 1), ~0ull, nullptr, nullptr);
+    if (rc) return rc;
+    PPO_CUDA(cudaMemsetAsync(t->next_done, 0, (size_t)N * 4, nullptr));
+    PPO_CUDA(cudaDeviceSynchronize());
+    return PPO_OK;
+}
+
+// ---- phases ---------------------------------------------------------------------------------------
+// by-value kernel arguments are snapshotted at launch, so back-to-back asynchronous iterations
+// cannot race on a staging buffer
+__global__ void set_scalars_kernel(Scalars* dst, Scalars v) { *dst = v; }
+static int push_scalars(ppo_trainer* t, float lr, cudaStream_t st) {
+    Scalars v;
+    v.rollout_counter = t->rollout_counter;
+    v.epoch_counter = t->epoch_counter;
+    v.step_base = t->step;
+    v.lr = lr;
+    v.pad = 0.0f;
+    set_scalars_kernel<<<1, 1, 0, st>>>(t->d_scal, v);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
+static int phase_rollout(ppo_trainer* t, cudaStream_t st) {
+    const ppo_trainer_cfg& c = t->cfg;
+    PPO_CUDA(cudaMemsetAsync(t->ep_stats, 0, 3 * 8, st));
+    ppo_rollout_cfg rc{};
+    rc.env_kind = c.env_kind; rc.n_envs = c.num_envs; rc.n_steps = c.num_steps;
+    rc.max_episode_steps = c.max_episode_steps; rc.gamma = c.gamma; rc.gae_lambda = c.gae_lambda;
+    rc.use_gae = c.use_gae; rc.entropy_mode = c.hyper.entropy_mode; rc.masked = c.masked;
+    rc.env_id_base = (uint32_t)c.rank * (uint32_t)c.num_envs; rc.seed = c.seed;
+    rc.counter = 0; rc.d_counter = &t->d_scal->rollout_counter;
+    return ppo_rollout(t->params, &c.dims, &rc, t->state, t->ep_len, t->ep_ret, t->next_done, t->next_value, t->obs,
+                       t->actions, t->logprobs, t->rewards, t->dones, t->values, t->adv, t->ret, t->masks,
+                       t->ep_stats, st);
+}
+
+static int phase_begin_epoch(ppo_trainer* t, int epoch, cudaStream_t st) {
+    const ppo_trainer_cfg& c = t->cfg;
+    // rank-salted seed: every rank permutes its own shard independently
+    int rc = ppo_make_permutation(t->B, c.seed ^ (0xA5A5A5A5ull * (uint64_t)(c.rank + 1)), (uint64_t)epoch,
+                                  &t->d_scal->epoch_counter, t->perm, st);
+    if (rc) return rc;
+    if (!c.hyper.norm_adv) return PPO_OK;
+    if (c.world_size > 1 && t->comm) {
+        rc = ppo_adv_stats(t->adv, t->perm, t->B, t->mb_size, t->n_mb, nullptr, t->adv_partial, st);
+        if (rc) return rc;
+        rc = ppo_comm_allreduce_f64(t->comm, t->adv_partial, (int64_t)t->n_mb * 3, st);
+        if (rc) return rc;
+        return ppo_adv_stats_finalize(t->adv_partial, t->n_mb, t->adv_stats, st);
+    }
+    return ppo_adv_stats(t->adv, t->perm, t->B, t->mb_size, t->n_mb, t->adv_stats, nullptr, st);
+}
+
+static int phase_minibatch_grads(ppo_trainer* t, int mb, cudaStream_t st) {
+    const ppo_trainer_cfg& c = t->cfg;
+    const int64_t start = (int64_t)mb * t->mb_size;
+    int64_t cnt = t->B - start;
+    if (cnt > t->mb_size) cnt = t->mb_size;
+    PPO_REQUIRE(cnt >= 1, "minibatch %d is empty", mb);
+    const float inv_n = 1.0f / ((float)cnt * (float)c.world_size);
+    return ppo_update_minibatch(t->params, &c.dims, t->obs, t->masks, t->actions, t->logprobs, t->adv, t->ret,
+                                t->values, t->perm, start, (int)cnt, inv_n, t->adv_stats + 2 * mb, &c.hyper, t->upd_ws,
+                                t->grads, t->grads + t->P, st);
+}
+
+static int phase_apply(ppo_trainer* t, cudaStream_t st) {
+    const ppo_trainer_cfg& c = t->cfg;
+    if (c.world_size > 1 && t->comm) {
+        int rc = ppo_comm_allreduce_f32(t->comm, t->grads, (int64_t)t->P + 8, st);
+        if (rc) return rc;
+    }
+    const int k = t->opt_in_iter++;
+    PPO_REQUIRE(k < t->n_opt, "more optimiser steps than update_epochs * num_minibatches in one iteration");
+    return clip_adamw_launch(t->params, t->grads, t->exp_avg, t->exp_avg_sq, t->P, 0.0f, &t->d_scal->lr, c.beta1,
+                             c.beta2, c.adam_eps, c.weight_decay, (int64_t)k + 1, &t->d_scal->step_base,
+                             c.max_grad_norm, 1.0f, t->norm_out, t->grads + t->P, t->diag_hist + (size_t)k * 8, st);
+}
+
+static int phase_tail(ppo_trainer* t, cudaStream_t st) {
+    int rc = ppo_explained_variance(t->B, t->ret, t->values, t->ev_ws, t->ev_out, st);
+    if (rc) return rc;
+    if (t->n_opt > 0)
+        PPO_CUDA(cudaMemcpyAsync(t->h_diag, t->diag_hist, (size_t)t->n_opt * 32, cudaMemcpyDeviceToHost, st));
+    PPO_CUDA(cudaMemcpyAsync(&t->h_rb->ev, t->ev_out, 4, cudaMemcpyDeviceToHost, st));
+    PPO_CUDA(cudaMemcpyAsync(&t->h_rb->grad_norm, t->norm_out, 4, cudaMemcpyDeviceToHost, st));
+    PPO_CUDA(cudaMemcpyAsync(t->h_rb->ep_stats, t->ep_stats, 24, cudaMemcpyDeviceToHost, st));
+    return PPO_OK;
+}
+
+static int enqueue_iteration(ppo_trainer* t, cudaStream_t st) {
+    int rc;
+    t->opt_in_iter = 0;
+    if ((rc = phase_rollout(t, st))) return rc;
+    for (int e = 0; e < t->cfg.update_epochs; e++) {
+        if ((rc = phase_begin_epoch(t, e, st))) return rc;
+        for (int mb = 0; mb < t->n_mb; mb++) {
+            if ((rc = phase_minibatch_grads(t, mb, st))) return rc;
+            if ((rc = phase_apply(t, st))) return rc;
+        }
+    }
+    return phase_tail(t, st);
+}
+
+static void advance_counters(ppo_trainer* t) {
+    t->rollout_counter += (uint64_t)t->cfg.num_steps;
+    t->epoch_counter += (uint64_t)t->cfg.update_epochs;
+    t->step += t->n_opt;
+}
+
+static void fill_result(ppo_trainer* t, float lr, ppo_iter_result* r) {
+    memset(r, 0, sizeof(*r));
+    if (t->n_opt > 0) {
+        const float* last = t->h_diag + (size_t)(t->n_opt - 1) * 8;
+        r->pg_loss = last[0]; r->v_loss = last[1]; r->entropy = last[2]; r->loss = last[3]; r->approx_kl = last[4];
+        double cf = 0.0;  // clip_fraction = mean over all minibatches of the update (Utils.cpp:5-14)
+        for (int k = 0; k < t->n_opt; k++) cf += t->h_diag[(size_t)k * 8 + 5];
+        r->clipfrac = (float)(cf / t->n_opt);
+    }
+    r->explained_variance = t->h_rb->ev;
+    r->grad_norm = t->h_rb->grad_norm;
+    r->episodes = t->h_rb->ep_stats[0];
+    r->ep_len_sum = t->h_rb->ep_stats[1];
+    r->ep_ret_sum = t->h_rb->ep_stats[2];
+    r->lr = lr;
+}
+
+extern "C" int ppo_trainer_iterate(ppo_trainer* t, float h_lr, ppo_iter_result* h_result, ppo_stream_t stream) {
+    PPO_REQUIRE(t, "null trainer");
+    cudaStream_t st = as_stream(stream);
+    int rc;
+    if ((rc = push_scalars(t, h_lr, st))) return rc;
+    if (t->cfg.use_cuda_graph) {
+        if (t->graph_exec && t->graph_stream != st) {  // a graph is tied to nothing, but keep it simple
+            cudaGraphExecDestroy(t->graph_exec);
+            t->graph_exec = nullptr;
+        }
+        if (!t->graph_exec) {
+            cudaGraph_t g = nullptr;
+            PPO_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            rc = enqueue_iteration(t, st);
+            cudaError_t e = cudaStreamEndCapture(st, &g);
+            if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+            PPO_CUDA(e);
+            PPO_CUDA(cudaGraphInstantiate(&t->graph_exec, g, 0));
+            cudaGraphDestroy(g);
+            t->graph_stream = st;
+        }
+        PPO_CUDA(cudaGraphLaunch(t->graph_exec, st));
+    } else {
+        if ((rc = enqueue_iteration(t, st))) return rc;
+    }
+    advance_counters(t);
+    if (h_result) {
+        PPO_CUDA(cudaStreamSynchronize(st));
+        fill_result(t, h_lr, h_result);
+    }
+    return PPO_OK;
+}
+
+// ---- split-phase API (host loops that interleave their own work between phases) ---------------------
+extern "C" int ppo_trainer_rollout(ppo_trainer* t, float h_lr, ppo_stream_t stream) {
+    PPO_REQUIRE(t, "null trainer");
+    int rc = push_scalars(t, h_lr, as_stream(stream));
+    if (rc) return rc;
+    t->opt_in_iter = 0;
+    return phase_rollout(t, as_stream(stream));
+}
+extern "C" int ppo_trainer_begin_epoch(ppo_trainer* t, int epoch, ppo_stream_t stream) {
+    PPO_REQUIRE(t && epoch >= 0, "bad argument");
+    return phase_begin_epoch(t, epoch, as_stream(stream));
+}
+extern "C" int ppo_trainer_minibatch_grads(ppo_trainer* t, int mb, ppo_stream_t stream) {
+    PPO_REQUIRE(t && mb >= 0 && mb < t->n_mb, "minibatch index out of range");
+    return phase_minibatch_grads(t, mb, as_stream(stream));
+}
+extern "C" int ppo_trainer_apply(ppo_trainer* t, ppo_stream_t stream) {
+    PPO_REQUIRE(t, "null trainer");
+    return phase_apply(t, as_stream(stream));
+}
+extern "C" int ppo_trainer_finish(ppo_trainer* t, float h_lr, ppo_iter_result* h_result, ppo_stream_t stream) {
+    PPO_REQUIRE(t, "null trainer");
+    cudaStream_t st = as_stream(stream);
+    int rc = phase_tail(t, st);
+    if (rc) return rc;
+    // counters advance by what was actually issued
+    t->rollout_counter += (uint64_t)t->cfg.num_steps;
+    t->epoch_counter += (uint64_t)t->cfg.update_epochs;
+    t->step += t->opt_in_iter;
+    if (h_result) {
+        PPO_CUDA(cudaStreamSynchronize(st));
+        fill_result(t, h_lr, h_result);
+    }
+    return PPO_OK;
+}

@@ -1,0 +1,296 @@
+// update.cu — K5: fused minibatch forward + PPO loss + closed-form backward (fp32 FMA path).
+// Replaces PPO/PPO_Discrete.cpp:579-638 (forward with stored actions, ratio, clipped surrogate,
+// clipped value loss, entropy bonus, autograd backward): ~100 LibTorch op dispatches + the autograd
+// graph become two launches (tile kernel + deterministic cross-CTA reduction).
+//
+// Each persistent CTA walks tiles of TM minibatch rows gathered through the permutation:
+//   actor : forward -> per-row Categorical(Masked) log-prob / entropy / ratio -> dL/dlogits -> backward
+//   critic: forward -> per-row (clipped) value loss -> dL/dv -> backward
+// (the two nets are disjoint graphs, so they reuse the same two activation buffers).
+// Weight-gradient partials accumulate in a per-CTA slab of `workspace`; reduce_kernel sums the
+// slabs in CTA order (no atomics: results are run-to-run identical) and finishes the diagnostics.
+#include "policy.cuh"
+
+namespace ppo {
+
+constexpr int UPD_MAX_GRID = 296;  // 2 CTAs x 148 SMs
+constexpr int UPD_NDIAG = 8;       // pg, v, ent, kl, clip (+3 spare) partial sums per CTA
+
+__host__ __device__ inline int64_t slab_stride(int P) { return ((int64_t)P + 31) & ~(int64_t)31; }
+
+struct UpdArgs {
+    const float* params;
+    Dims d;
+    const float* obs;
+    const uint8_t* mask;
+    const int32_t* actions;
+    const float* old_logprob;
+    const float* adv;
+    const float* ret;
+    const float* old_val;
+    const int32_t* perm;
+    int64_t mb_start;
+    int mb_size;
+    float inv_n;
+    const float* adv_stats;  // {mean, std} or nullptr
+    ppo_hyper hp;
+    float* slabs;    // [grid][slab_stride(P)]
+    double* dpart;   // [grid][UPD_NDIAG]
+};
+
+template <int TM, int H>
+__device__ inline void net_backward(float* sm, const TileLayout& L, int O, const float* __restrict__ params,
+                                    const NetOff& off, int K3, const float* dOut, int ldo, int rows,
+                                    float* __restrict__ g) {
+    // dOut rows >= `rows` are zero, so every dZ below is zero there too.
+    layer3_bwd_dw<TM, H>(sm + L.a2, K3, dOut, ldo, rows, g + off.W3, g + off.b3);
+    __syncthreads();
+    layer3_bwd_dx<TM, H>(sm + L.a2, params + off.W3, K3, dOut, ldo);
+    __syncthreads();
+    layer2_bwd_dw<TM, H>(sm + L.a2, sm + L.a1, g + off.W2, g + off.b2);
+    layer2_bwd_dx<TM, H>(sm + L.a2, params + off.W2, sm + L.a1, sm + L.ws);
+    layer1_bwd_dw<TM, H>(sm + L.a1, sm + L.xs, O, g + off.W1, g + off.b1);
+    __syncthreads();
+}
+
+template <int TM, int H>
+__global__ void __launch_bounds__(MLP_THREADS) update_kernel(const UpdArgs a) {
+    extern __shared__ __align__(16) float sm[];
+    const int O = a.d.O, K = a.d.K, heads = a.d.heads;
+    const TileLayout L = tile_layout(TM, H, O, K);
+    int64_t* sidx = reinterpret_cast<int64_t*>(sm + ((L.end + 1) & ~1));  // [TM] gathered row index
+    const NetOff co = critic_off(O, H), ao = actor_off(O, H, K);
+    const int P = num_params(O, H, K);
+    float* g = a.slabs + (size_t)blockIdx.x * slab_stride(P);
+    for (int i = threadIdx.x; i < P; i += MLP_THREADS) g[i] = 0.0f;
+
+    const bool masked = a.mask != nullptr;
+    const float c = a.hp.clip_coef, lo = 1.0f - c, hi = 1.0f + c;
+    float meanf = 0.0f, stdf = 1.0f;
+    if (a.hp.norm_adv) { meanf = a.adv_stats[0]; stdf = a.adv_stats[1]; }
+    double s_pg = 0.0, s_v = 0.0, s_ent = 0.0, s_kl = 0.0, s_clip = 0.0;
+
+    const int ntiles = (a.mb_size + TM - 1) / TM;
+    const int t = threadIdx.x;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int r0 = tile * TM;
+        const int rows = min(TM, a.mb_size - r0);
+        __syncthreads();
+        if (t < TM) {
+            int64_t idx = -1;
+            if (t < rows) idx = a.perm ? (int64_t)a.perm[a.mb_start + r0 + t] : a.mb_start + r0 + t;
+            sidx[t] = idx;
+        }
+        __syncthreads();
+        for (int e = t; e < TM * O; e += MLP_THREADS) {
+            const int m = e / O, i = e % O;
+            sm[L.xs + e] = (m < rows) ? __ldg(a.obs + sidx[m] * O + i) : 0.0f;
+        }
+        __syncthreads();
+
+        // ---------------- actor: forward, loss terms, dL/dlogits (in place over the logits) ----------
+        net_forward<TM, H>(sm, L, O, a.params, ao, K, sm + L.ls, L.ldo);
+        if (t < TM) {
+            float* x = sm + L.ls + t * L.ldo;
+            if (t < rows) {
+                const int64_t r = sidx[t];
+                const uint64_t mbits = masked ? pack_mask(a.mask + r * K, K) : ~0ull;
+                const int32_t* act = a.actions + r * heads;
+                // pass 1: log-prob of the stored actions + entropy, summed over heads (Agent.cpp:168)
+                float newlogp = 0.0f, ent = 0.0f;
+                float hent[PPO_MAX_HEADS];
+                HeadStats hs[PPO_MAX_HEADS];
+                int off = 0;
+                for (int h = 0; h < heads; h++) {
+                    const int Kh = a.d.nvec[h];
+                    const uint64_t mb = mbits >> off;
+                    hs[h] = head_stats(x + off, Kh, mb, masked);
+                    const int aa = act[h];
+                    newlogp = __fadd_rn(newlogp,
+                                        head_logp(masked_logit(x[off + aa], !masked || ((mb >> aa) & 1ull)), hs[h]));
+                    hent[h] = head_entropy(x + off, Kh, mb, masked, hs[h], a.hp.entropy_mode);
+                    ent = __fadd_rn(ent, hent[h]);
+                    off += Kh;
+                }
+                const float logratio = newlogp - __ldg(a.old_logprob + r);  // :585
+                const float ratio = expf(logratio);                         // :586
+                s_kl += (double)((ratio - 1.0f) - logratio);                // :352
+                if (fabsf(ratio - 1.0f) > c) s_clip += 1.0;                 // :348
+                float A = __ldg(a.adv + r);
+                if (a.hp.norm_adv) A = __fdiv_rn(A - meanf, stdf + 1e-8f);  // :591-594
+                const float rc = ratio < lo ? lo : (ratio > hi ? hi : ratio);
+                const float pg1 = -A * ratio, pg2 = -A * rc;                // :597-598
+                s_pg += (double)(pg1 > pg2 ? pg1 : pg2);
+                s_ent += (double)ent;
+                // d pg / d ratio: ATen max splits ties 1/2-1/2, clamp's mask is inclusive (SURVEY §8 a-bis)
+                float dpg_dr;
+                if (ratio >= lo && ratio <= hi) dpg_dr = -A;
+                else if (pg1 > pg2) dpg_dr = -A;
+                else if (pg1 == pg2) dpg_dr = -0.5f * A;
+                else dpg_dr = 0.0f;
+                const float g_logp = a.inv_n * dpg_dr * ratio;
+                const bool exact = masked || a.hp.entropy_mode == PPO_ENTROPY_EXACT;
+                const float ge = a.hp.ent_coef * a.inv_n;
+                off = 0;
+                for (int h = 0; h < heads; h++) {
+                    const int Kh = a.d.nvec[h];
+                    const uint64_t mb = mbits >> off;
+                    const int aa = act[h];
+                    for (int j = 0; j < Kh; j++) {
+                        const bool valid = !masked || ((mb >> j) & 1ull);
+                        const float xm = masked_logit(x[off + j], valid);
+                        const float p = head_prob(xm, hs[h]);
+                        float dz = g_logp * ((j == aa ? 1.0f : 0.0f) - p);
+                        if (exact && ge != 0.0f && p > 0.0f) dz += ge * p * (head_logp(xm, hs[h]) + hent[h]);
+                        if (!valid) dz = 0.0f;
+                        x[off + j] = dz;
+                    }
+                    off += Kh;
+                }
+            } else {
+                for (int j = 0; j < K; j++) x[j] = 0.0f;
+            }
+        }
+        __syncthreads();
+        net_backward<TM, H>(sm, L, O, a.params, ao, K, sm + L.ls, L.ldo, rows, g);
+
+        // ---------------- critic: forward, value loss, dL/dv ----------------------------------------
+        net_forward<TM, H>(sm, L, O, a.params, co, 1, sm + L.vs, 1);
+        if (t < TM) {
+            float gv = 0.0f;
+            if (t < rows) {
+                const int64_t r = sidx[t];
+                const float value = sm[L.vs + t];
+                const float R = __ldg(a.ret + r);
+                const float du = value - R;
+                const float u = du * du;
+                float dv;
+                if (a.hp.clip_vloss) {  // :603-618
+                    const float vo = __ldg(a.old_val + r);
+                    const float dvo = value - vo;
+                    const float dcl = dvo < -c ? -c : (dvo > c ? c : dvo);
+                    const float vc = vo + dcl;
+                    const float w = (vc - R) * (vc - R);
+                    s_v += (double)(u > w ? u : w);
+                    const float dw = (dvo >= -c && dvo <= c) ? (vc - R) : 0.0f;
+                    dv = (u > w) ? du : ((w > u) ? dw : 0.5f * du + 0.5f * dw);
+                } else {  // :621-625
+                    s_v += (double)u;
+                    dv = du;
+                }
+                gv = a.hp.vf_coef * a.inv_n * dv;
+            }
+            sm[L.vs + t] = gv;
+        }
+        __syncthreads();
+        net_backward<TM, H>(sm, L, O, a.params, co, 1, sm + L.vs, 1, rows, g);
+    }
+
+    // per-CTA diagnostic partial sums (only threads < TM hold non-zero values)
+    __syncthreads();
+    double* red = reinterpret_cast<double*>(sm);  // reuse: 5 x TM doubles
+    if (t < TM) {
+        red[0 * TM + t] = s_pg; red[1 * TM + t] = s_v; red[2 * TM + t] = s_ent;
+        red[3 * TM + t] = s_kl; red[4 * TM + t] = s_clip;
+    }
+    __syncthreads();
+    if (t < 5) {
+        double acc = 0.0;
+        for (int m = 0; m < TM; m++) acc += red[t * TM + m];
+        a.dpart[(size_t)blockIdx.x * UPD_NDIAG + t] = acc;
+    }
+}
+
+// grads_out[i] = sum over CTAs (fixed order, double accumulation) of slab[cta][i]; the last block also
+// turns the diagnostic partials into diag_out = {pg_loss, v_loss, entropy, loss, approx_kl, clipfrac, 0, 0}.
+__global__ void __launch_bounds__(256) reduce_kernel(const float* __restrict__ slabs, const double* __restrict__ dpart,
+                                                     int nslabs, int P, int64_t stride, float inv_n, float ent_coef,
+                                                     float vf_coef, float* __restrict__ grads_out,
+                                                     float* __restrict__ diag_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < P) {
+        double acc = 0.0;
+        for (int s = 0; s < nslabs; s++) acc += (double)slabs[(size_t)s * stride + i];
+        grads_out[i] = (float)acc;
+    }
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x < 32 && diag_out) {
+        double v = 0.0;
+        if (threadIdx.x < 5)
+            for (int s = 0; s < nslabs; s++) v += dpart[(size_t)s * UPD_NDIAG + threadIdx.x];
+        const double n_inv = (double)inv_n;
+        const float pg = (float)(__shfl_sync(0xffffffffu, v, 0) * n_inv);
+        const float vl = 0.5f * (float)(__shfl_sync(0xffffffffu, v, 1) * n_inv);
+        const float en = (float)(__shfl_sync(0xffffffffu, v, 2) * n_inv);
+        const float kl = (float)(__shfl_sync(0xffffffffu, v, 3) * n_inv);
+        const float cf = (float)(__shfl_sync(0xffffffffu, v, 4) * n_inv);
+        if (threadIdx.x == 0) {
+            diag_out[0] = pg; diag_out[1] = vl; diag_out[2] = en;
+            diag_out[3] = pg - ent_coef * en + vl * vf_coef;  // :631
+            diag_out[4] = kl; diag_out[5] = cf; diag_out[6] = 0.0f; diag_out[7] = 0.0f;
+        }
+    }
+}
+
+template <int TM, int H>
+static int launch_update(const UpdArgs& a, float* grads_out, float* diag_out, cudaStream_t st) {
+    const TileLayout L = tile_layout(TM, H, a.d.O, a.d.K);
+    const size_t smem = (size_t)(((L.end + 1) & ~1) + 2 * TM) * sizeof(float);
+    static bool attr_done = false;
+    if (!attr_done) {
+        PPO_CUDA(cudaFuncSetAttribute(update_kernel<TM, H>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_done = true;
+    }
+    PPO_REQUIRE(smem <= 200 * 1024, "update: tile needs %zu B of shared memory", smem);
+    const int ntiles = (a.mb_size + TM - 1) / TM;
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    int grid = 2 * sms < UPD_MAX_GRID ? 2 * sms : UPD_MAX_GRID;
+    if (ntiles < grid) grid = ntiles;
+    update_kernel<TM, H><<<grid, MLP_THREADS, smem, st>>>(a);
+    PPO_LAUNCH_CHECK();
+    const int P = num_params(a.d.O, a.d.H, a.d.K);
+    reduce_kernel<<<(P + 255) / 256, 256, 0, st>>>(a.slabs, a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef,
+                                                   a.hp.vf_coef, grads_out, diag_out);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
+}  // namespace ppo
+
+using namespace ppo;
+
+extern "C" int64_t ppo_update_workspace_bytes(const ppo_dims* dims) {
+    Dims d;
+    if (make_dims(dims, &d)) return -1;
+    const int P = num_params(d.O, d.H, d.K);
+    return (int64_t)UPD_MAX_GRID * (slab_stride(P) * (int64_t)sizeof(float) + UPD_NDIAG * (int64_t)sizeof(double));
+}
+
+extern "C" int ppo_update_minibatch(const float* params, const ppo_dims* dims, const float* obs, const uint8_t* mask,
+                                    const int32_t* actions, const float* old_logprob, const float* adv,
+                                    const float* ret, const float* old_val, const int32_t* perm, int64_t mb_start,
+                                    int mb_size, float inv_n, const float* adv_stats, const ppo_hyper* h_hyper,
+                                    void* workspace, float* grads_out, float* diag_out, ppo_stream_t stream) {
+    UpdArgs a{};
+    if (int rc = make_dims(dims, &a.d)) return rc;
+    PPO_REQUIRE(params && obs && actions && old_logprob && adv && ret && h_hyper && workspace && grads_out,
+                "ppo_update_minibatch: null buffer");
+    PPO_REQUIRE(mb_size >= 1 && mb_start >= 0, "ppo_update_minibatch: mb_start=%lld mb_size=%d",
+                (long long)mb_start, mb_size);
+    PPO_REQUIRE(!h_hyper->clip_vloss || old_val, "ppo_update_minibatch: clip_vloss needs old_val");
+    PPO_REQUIRE(!h_hyper->norm_adv || adv_stats, "ppo_update_minibatch: norm_adv needs adv_stats");
+    a.params = params; a.obs = obs; a.mask = mask; a.actions = actions; a.old_logprob = old_logprob;
+    a.adv = adv; a.ret = ret; a.old_val = old_val; a.perm = perm; a.mb_start = mb_start; a.mb_size = mb_size;
+    a.inv_n = inv_n; a.adv_stats = adv_stats; a.hp = *h_hyper;
+    const int P = num_params(a.d.O, a.d.H, a.d.K);
+    a.slabs = reinterpret_cast<float*>(workspace);
+    a.dpart = reinterpret_cast<double*>(reinterpret_cast<char*>(workspace) +
+                                        (size_t)UPD_MAX_GRID * slab_stride(P) * sizeof(float));
+    cudaStream_t st = as_stream(stream);
+    switch (a.d.H) {
+        case 64: return launch_update<64, 64>(a, grads_out, diag_out, st);
+        case 128: return launch_update<32, 128>(a, grads_out, diag_out, st);
+        case 256: return launch_update<32, 256>(a, grads_out, diag_out, st);
+    }
+    set_error("hidden=%d unsupported", a.d.H);
+    return PPO_ERR_UNSUPPORTED;
+}
