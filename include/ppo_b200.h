@@ -262,6 +262,14 @@ int ppo_trainer_minibatch_grads(ppo_trainer* t, int mb, ppo_stream_t stream);
 int ppo_trainer_apply(ppo_trainer* t, ppo_stream_t stream); /* [allreduce] + clip + AdamW */
 int ppo_trainer_finish(ppo_trainer* t, float h_lr, ppo_iter_result* h_result, ppo_stream_t stream);
 
+/* Per-phase device timing for bench.py: profile(1) brackets every phase of later iterations with a
+ * cudaEvent pair on its launch stream (CUDA-graph replay is bypassed meanwhile); phase_ms
+ * synchronises, writes accumulated milliseconds / launch counts for the 6 phases {rollout, gae,
+ * epoch setup (permutation + advantage statistics), update (K5), apply (allreduce + K6), tail} and
+ * resets the accumulators. */
+int ppo_trainer_profile(ppo_trainer* t, int enable);
+int ppo_trainer_phase_ms(ppo_trainer* t, float* h_ms6, int32_t* h_count6);
+
 /* ---- data parallelism (new: the reference is single-device, PPO/PPO_Discrete.cpp:65) ------- */
 /* One process per GPU.  Envs shard by rank; parameters and Adam moments are replicated; per
  * minibatch the gradient slab (+8 diagnostics) is allreduced, per epoch the advantage moments.

@@ -72,13 +72,47 @@ struct ppo_trainer {
     cudaGraphExec_t graph_exec = nullptr;
     cudaStream_t graph_stream = nullptr;
     int opt_in_iter = 0;  // optimiser steps issued in the current iteration (split-phase API)
+    // optional per-phase device timing (cudaEvent pairs on the launch stream; eager mode only)
+    bool profile = false;
+    std::vector<cudaEvent_t> ev_pool;
+    std::vector<int> ev_phase;  // phase of pair i (events 2i, 2i+1)
+    size_t ev_used = 0;
 };
+
+enum { PH_ROLLOUT = 0, PH_GAE, PH_EPOCH, PH_UPDATE, PH_APPLY, PH_TAIL, PH_COUNT };
+
+namespace {
+struct PhaseTimer {  // records an event pair around a phase when profiling is on
+    ppo_trainer* t;
+    cudaStream_t st;
+    bool on;
+    PhaseTimer(ppo_trainer* t_, int phase, cudaStream_t st_) : t(t_), st(st_), on(t_->profile) {
+        if (!on) return;
+        if (t->ev_used + 2 > t->ev_pool.size()) {
+            cudaEvent_t a, b;
+            cudaEventCreate(&a);
+            cudaEventCreate(&b);
+            t->ev_pool.push_back(a);
+            t->ev_pool.push_back(b);
+        }
+        t->ev_phase.resize(t->ev_used / 2 + 1);
+        t->ev_phase[t->ev_used / 2] = phase;
+        cudaEventRecord(t->ev_pool[t->ev_used], st);
+    }
+    ~PhaseTimer() {
+        if (!on) return;
+        cudaEventRecord(t->ev_pool[t->ev_used + 1], st);
+        t->ev_used += 2;
+    }
+};
+}  // namespace
 
 static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 extern "C" void ppo_trainer_destroy(ppo_trainer* t) {
     if (!t) return;
     if (t->graph_exec) cudaGraphExecDestroy(t->graph_exec);
+    for (cudaEvent_t e : t->ev_pool) cudaEventDestroy(e);
     if (t->arena) cudaFree(t->arena);
     if (t->h_diag) cudaFreeHost(t->h_diag);
     if (t->h_rb) cudaFreeHost(t->h_rb);
@@ -251,13 +285,21 @@ static int phase_rollout(ppo_trainer* t, cudaStream_t st) {
     rc.use_gae = c.use_gae; rc.entropy_mode = c.hyper.entropy_mode; rc.masked = c.masked;
     rc.env_id_base = (uint32_t)c.rank * (uint32_t)c.num_envs; rc.seed = c.seed;
     rc.counter = 0; rc.d_counter = &t->d_scal->rollout_counter;
-    return ppo_rollout(t->params, &c.dims, &rc, t->state, t->ep_len, t->ep_ret, t->next_done, t->next_value, t->obs,
-                       t->actions, t->logprobs, t->rewards, t->dones, t->values, t->adv, t->ret, t->masks,
-                       t->ep_stats, st);
+    {
+        PhaseTimer pt(t, PH_ROLLOUT, st);
+        int r = ppo_rollout(t->params, &c.dims, &rc, t->state, t->ep_len, t->ep_ret, t->next_done, t->next_value,
+                            t->obs, t->actions, t->logprobs, t->rewards, t->dones, t->values, nullptr, nullptr,
+                            t->masks, t->ep_stats, st);
+        if (r) return r;
+    }
+    PhaseTimer pt(t, PH_GAE, st);
+    return ppo_gae(c.num_steps, c.num_envs, t->rewards, t->values, t->dones, t->next_value, t->next_done, c.gamma,
+                   c.gae_lambda, c.use_gae, t->adv, t->ret, st);
 }
 
 static int phase_begin_epoch(ppo_trainer* t, int epoch, cudaStream_t st) {
     const ppo_trainer_cfg& c = t->cfg;
+    PhaseTimer pt(t, PH_EPOCH, st);
     // rank-salted seed: every rank permutes its own shard independently
     int rc = ppo_make_permutation(t->B, c.seed ^ (0xA5A5A5A5ull * (uint64_t)(c.rank + 1)), (uint64_t)epoch,
                                   &t->d_scal->epoch_counter, t->perm, st);
@@ -280,6 +322,7 @@ static int phase_minibatch_grads(ppo_trainer* t, int mb, cudaStream_t st) {
     if (cnt > t->mb_size) cnt = t->mb_size;
     PPO_REQUIRE(cnt >= 1, "minibatch %d is empty", mb);
     const float inv_n = 1.0f / ((float)cnt * (float)c.world_size);
+    PhaseTimer pt(t, PH_UPDATE, st);
     return ppo_update_minibatch(t->params, &c.dims, t->obs, t->masks, t->actions, t->logprobs, t->adv, t->ret,
                                 t->values, t->perm, start, (int)cnt, inv_n, t->adv_stats + 2 * mb, &c.hyper, t->upd_ws,
                                 t->grads, t->grads + t->P, st);
@@ -287,6 +330,7 @@ static int phase_minibatch_grads(ppo_trainer* t, int mb, cudaStream_t st) {
 
 static int phase_apply(ppo_trainer* t, cudaStream_t st) {
     const ppo_trainer_cfg& c = t->cfg;
+    PhaseTimer pt(t, PH_APPLY, st);
     if (c.world_size > 1 && t->comm) {
         int rc = ppo_comm_allreduce_f32(t->comm, t->grads, (int64_t)t->P + 8, st);
         if (rc) return rc;
@@ -299,6 +343,7 @@ static int phase_apply(ppo_trainer* t, cudaStream_t st) {
 }
 
 static int phase_tail(ppo_trainer* t, cudaStream_t st) {
+    PhaseTimer pt(t, PH_TAIL, st);
     int rc = ppo_explained_variance(t->B, t->ret, t->values, t->ev_ws, t->ev_out, st);
     if (rc) return rc;
     if (t->n_opt > 0)
@@ -351,7 +396,7 @@ extern "C" int ppo_trainer_iterate(ppo_trainer* t, float h_lr, ppo_iter_result* 
     cudaStream_t st = as_stream(stream);
     int rc;
     if ((rc = push_scalars(t, h_lr, st))) return rc;
-    if (t->cfg.use_cuda_graph) {
+    if (t->cfg.use_cuda_graph && !t->profile) {
         if (t->graph_exec && t->graph_stream != st) {  // a graph is tied to nothing, but keep it simple
             cudaGraphExecDestroy(t->graph_exec);
             t->graph_exec = nullptr;
@@ -412,5 +457,29 @@ extern "C" int ppo_trainer_finish(ppo_trainer* t, float h_lr, ppo_iter_result* h
         PPO_CUDA(cudaStreamSynchronize(st));
         fill_result(t, h_lr, h_result);
     }
+    return PPO_OK;
+}
+
+// ---- per-phase device timing -------------------------------------------------------------------------
+// ppo_trainer_profile(t, 1) makes every later phase record a cudaEvent pair on its launch stream (graph
+// replay is bypassed while profiling).  ppo_trainer_phase_ms synchronises, returns the accumulated
+// milliseconds and launch counts per phase {rollout, gae, epoch setup, update, apply, tail} and resets.
+extern "C" int ppo_trainer_profile(ppo_trainer* t, int enable) {
+    PPO_REQUIRE(t, "null trainer");
+    t->profile = enable != 0;
+    t->ev_used = 0;
+    return PPO_OK;
+}
+extern "C" int ppo_trainer_phase_ms(ppo_trainer* t, float* h_ms6, int32_t* h_count6) {
+    PPO_REQUIRE(t && h_ms6, "null argument");
+    PPO_CUDA(cudaDeviceSynchronize());
+    for (int i = 0; i < PH_COUNT; i++) { h_ms6[i] = 0.0f; if (h_count6) h_count6[i] = 0; }
+    for (size_t i = 0; i + 1 < t->ev_used; i += 2) {
+        float ms = 0.0f;
+        PPO_CUDA(cudaEventElapsedTime(&ms, t->ev_pool[i], t->ev_pool[i + 1]));
+        h_ms6[t->ev_phase[i / 2]] += ms;
+        if (h_count6) h_count6[t->ev_phase[i / 2]] += 1;
+    }
+    t->ev_used = 0;
     return PPO_OK;
 }

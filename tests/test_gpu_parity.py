@@ -1,0 +1,546 @@
+"""GPU parity tests: every sm_100a kernel, called through the C ABI (libppo_b200.so), against the CPU oracle
+(oracle/ppo_oracle.c) on the same seeded inputs, and against the committed golden fixtures generated from the
+compiled reference (tests/golden/).  Tolerances are BASELINE.json's: env transitions 1e-6 rel (single step),
+identical actions on identical uniforms outside an epsilon band of a CDF edge, GAE 1e-5 rel, loss/gradients
+1e-4 rel (fp32 FMA path; only the summation order differs from the oracle's double accumulation)."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+FLT_MIN = np.float32(1.17549435e-38)
+
+
+@pytest.fixture(scope="module")
+def P():
+    import ppo_libtorch_b200 as p
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return p
+
+
+def dev(a, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.cuda().contiguous()
+
+
+def close(a, b, rtol, atol=0.0):
+    if isinstance(a, torch.Tensor):
+        a = a.cpu().numpy()
+    np.testing.assert_allclose(np.asarray(a, np.float64), np.asarray(b, np.float64), rtol=rtol, atol=atol)
+
+
+# ------------------------------------------------------------------------------------------------ envs
+@pytest.mark.parametrize("kind,name,S", [(0, "cartpole", 4), (1, "mountaincar", 2)])
+def test_env_step_golden(P, orc, golden, kind, name, S):
+    g = golden(name)
+    n = g["state"].shape[0]
+    state = dev(g["state"].T)                       # SoA [S,n]
+    ep_len = torch.zeros(n, dtype=torch.int32, device="cuda")
+    ep_ret = torch.zeros(n, dtype=torch.float32, device="cuda")
+    u = np.full((n, 4), 0.5, np.float32)
+    pre = state.clone()
+    obs, rew, done, fl, fr = P.ops.env_step(kind, state, ep_len, ep_ret, dev(g["action"], torch.int32), 10 ** 6,
+                                            reset_uniforms=dev(u))
+    term = g["terminated"].astype(bool)
+    # non-terminated envs: obs is the stepped state; terminated envs were auto-reset with u=0.5
+    close(obs.cpu().numpy()[~term], g["next_state"][~term], rtol=1e-6, atol=1e-7)
+    assert np.array_equal(rew.cpu().numpy(), g["reward"])
+    assert np.array_equal(done.cpu().numpy() > 0, term)
+    # against the oracle's vectorised step, including the reset branch
+    st = np.ascontiguousarray(pre.cpu().numpy().T)
+    o_len = np.zeros(n, np.int32)
+    o_ret = np.zeros(n, np.float32)
+    oobs, orew, odone, ofl, ofr = orc.env_step(kind, st, o_len, o_ret, g["action"].astype(np.int32), 10 ** 6, u)
+    close(obs, oobs, rtol=1e-6, atol=1e-7)
+    assert np.array_equal(done.cpu().numpy(), odone)
+    assert np.array_equal(fl.cpu().numpy(), ofl)
+    assert np.array_equal(ep_len.cpu().numpy(), o_len)
+    close(state.cpu().numpy().T, st, rtol=1e-6, atol=1e-7)
+
+
+def test_env_reset_seed2_known_answer(P, orc, golden):
+    """CartPole(seed=2).reset() stream of the shipped toml, through injected uniforms."""
+    g = golden("cartpole")
+    u = orc.mt19937_canonical(2, 32).reshape(8, 4)
+    state, ep_len, ep_ret, obs = P.ops.env_reset(P.ENV_CARTPOLE, 8, uniforms=dev(u))
+    assert np.array_equal(obs.cpu().numpy(), g["resets_seed2"])
+    assert np.array_equal(state.cpu().numpy().T, g["resets_seed2"])
+    assert ep_len.sum().item() == 0
+
+
+@pytest.mark.parametrize("n", [1, 3, 8, 1000, 4096])
+def test_env_vectorised_truncation_autoreset(P, orc, n):
+    """stepEnvs semantics (truncation at max_episode_steps, auto-reset, episode stats) vs the oracle, 40 steps,
+    ragged sizes (n not a multiple of the vector width)."""
+    rng = np.random.default_rng(n)
+    for kind, S, A in ((0, 4, 2), (1, 2, 3)):
+        u0 = rng.uniform(size=(n, 4)).astype(np.float32)
+        state, ep_len, ep_ret, obs = P.ops.env_reset(kind, n, uniforms=dev(u0))
+        st = np.ascontiguousarray(state.cpu().numpy().T)
+        o_len = np.zeros(n, np.int32)
+        o_ret = np.zeros(n, np.float32)
+        ndone = 0
+        for step in range(40):
+            act = rng.integers(0, A, n).astype(np.int32)
+            u = rng.uniform(size=(n, 4)).astype(np.float32)
+            obs, rew, done, fl, fr = P.ops.env_step(kind, state, ep_len, ep_ret, dev(act), 7, reset_uniforms=dev(u))
+            oobs, orew, odone, ofl, ofr = orc.env_step(kind, st, o_len, o_ret, act, 7, u)
+            close(obs, oobs, rtol=1e-6, atol=1e-7)
+            assert np.array_equal(rew.cpu().numpy(), orew)
+            assert np.array_equal(done.cpu().numpy(), odone)
+            assert np.array_equal(fl.cpu().numpy(), ofl)
+            close(fr, ofr, rtol=1e-6)
+            assert np.array_equal(ep_len.cpu().numpy(), o_len)
+            ndone += int(odone.sum())
+            st[:] = obs.cpu().numpy()          # re-sync so fp drift cannot build up
+        assert ndone >= 5 * n                  # truncation at 7 steps fired
+
+
+def test_env_philox_resets(P):
+    """without injected uniforms the reset draws come from Philox(seed, env, counter): check the stream."""
+    from philox_np import reset_uniforms
+    n = 257
+    state, ep_len, ep_ret, obs = P.ops.env_reset(P.ENV_CARTPOLE, n, seed=1234, counter=77)
+    u = reset_uniforms(1234, np.arange(n), 77)
+    expect = (u * (np.float32(0.05) - np.float32(-0.05)) + np.float32(-0.05)).astype(np.float32)
+    assert np.array_equal(obs.cpu().numpy(), expect)
+
+
+# --------------------------------------------------------------------------------------- distributions
+@pytest.mark.parametrize("K", [1, 2, 3, 7])
+def test_categorical_golden(P, golden, K):
+    g = golden("categorical")
+    a, lp, ent, probs = P.ops.categorical(dev(g[f"K{K}_logits"]), [K], actions=dev(g[f"K{K}_actions"], torch.int32),
+                                          want_probs=True)
+    close(probs, g[f"K{K}_probs"], rtol=4e-6, atol=1e-8)
+    close(lp, g[f"K{K}_logprob"], rtol=4e-6, atol=2e-6)
+    assert np.all(np.abs(ent.cpu().numpy() + FLT_MIN) < 1e-44)     # Q1 reproduced
+    _, _, ent_x = P.ops.categorical(dev(g[f"K{K}_logits"]), [K], actions=dev(g[f"K{K}_actions"], torch.int32),
+                                    entropy_mode=P.ENTROPY_EXACT)
+    p = g[f"K{K}_probs"].astype(np.float64)
+    close(ent_x, -(p * np.log(np.maximum(p, 1e-300))).sum(1), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("K", [3, 6, 21])
+def test_categorical_masked_golden(P, golden, K):
+    g = golden("categorical_masked")
+    a, lp, ent, probs = P.ops.categorical(dev(g[f"K{K}_logits"]), [K], mask=dev(g[f"K{K}_mask"]),
+                                          actions=dev(g[f"K{K}_actions"], torch.int32), want_probs=True)
+    close(probs, g[f"K{K}_probs"], rtol=4e-6, atol=1e-8)
+    close(lp, g[f"K{K}_logprob"], rtol=4e-6, atol=2e-6)
+    close(ent, g[f"K{K}_entropy"], rtol=1e-5, atol=2e-6)
+    assert np.all(probs.cpu().numpy()[g[f"K{K}_mask"] == 0] == 0)
+
+
+@pytest.mark.parametrize("n,nvec,masked", [(1, [2], False), (127, [1], False), (1000, [3], True),
+                                           (4099, [3, 3, 3, 3, 3, 2, 2, 2], True), (513, [64], True),
+                                           (262144, [3, 3, 3, 3, 3, 2, 2, 2], True)])
+def test_categorical_sampling_vs_oracle(P, orc, n, nvec, masked):
+    """identical uniforms -> identical actions except within eps of a CDF edge; logprob / entropy 1e-5."""
+    rng = np.random.default_rng(n + len(nvec))
+    K, heads = sum(nvec), len(nvec)
+    logits = rng.standard_normal((n, K)).astype(np.float32) * 2
+    mask = None
+    if masked:
+        mask = (rng.uniform(size=(n, K)) < 0.7).astype(np.uint8)
+        off = 0
+        for k in nvec:
+            mask[:, off] = 1          # >= 1 valid action per head
+            off += k
+    u = rng.uniform(size=(n, heads)).astype(np.float32)
+    a, lp, ent, probs = P.ops.categorical(dev(logits), nvec, mask=None if mask is None else dev(mask),
+                                          uniforms=dev(u), want_probs=True)
+    oa, olp, oent, oprobs, onl = orc.categorical(logits, nvec, mask=mask, uniforms=u, want_probs=True)
+    a = a.cpu().numpy()
+    close(probs, oprobs, rtol=4e-6, atol=1e-9)
+    # stated epsilon: a draw within 2^-22 of a CDF edge may fall either side
+    off, edge = 0, np.zeros((n, heads), bool)
+    for h, k in enumerate(nvec):
+        cdf = np.cumsum(oprobs[:, off:off + k].astype(np.float64), 1)
+        edge[:, h] = np.min(np.abs(cdf - u[:, h:h + 1]), 1) < 2.0 ** -22
+        off += k
+    diff = a != oa
+    assert np.all(~diff | edge), f"{diff.sum()} action mismatches outside the epsilon band"
+    same = ~diff.any(1)
+    close(lp.cpu().numpy()[same], olp[same], rtol=1e-5, atol=4e-6)
+    close(ent.cpu().numpy()[same], oent[same], rtol=1e-5, atol=4e-6)
+    if mask is not None:
+        off = 0
+        for h, k in enumerate(nvec):   # a masked action is never sampled
+            assert np.all(mask[np.arange(n), off + a[:, h]] == 1)
+            off += k
+    # evaluate mode on the sampled actions reproduces the log-probs
+    _, lp2, _ = P.ops.categorical(dev(logits), nvec, mask=None if mask is None else dev(mask), actions=dev(a))
+    assert torch.equal(lp2, lp)
+
+
+def test_categorical_philox_stream(P, orc):
+    """without injected uniforms the kernel draws Philox(seed, row, counter, head): same actions as the oracle
+    fed the numpy restatement of that stream."""
+    from philox_np import sample_uniforms
+    rng = np.random.default_rng(3)
+    nvec = [3, 3, 3, 3, 3, 2, 2, 2]
+    n = 2000
+    logits = rng.standard_normal((n, sum(nvec))).astype(np.float32)
+    a, lp, ent = P.ops.categorical(dev(logits), nvec, seed=99, counter=5)
+    u = sample_uniforms(99, np.arange(n), 5, len(nvec))
+    oa, olp, _ = orc.categorical(logits, nvec, uniforms=u)
+    assert (a.cpu().numpy() != oa).mean() < 1e-3
+
+
+# --------------------------------------------------------------------------------------- actor-critic
+@pytest.mark.parametrize("tag,O,nvec,masked", [("cartpole", 4, [2], False), ("cartpole_k1", 4, [1], False),
+                                               ("mountaincar", 2, [3], False),
+                                               ("multi", 2, [3, 3, 3, 3, 3, 2, 2, 2], True)])
+def test_policy_forward_golden(P, golden, tag, O, nvec, masked):
+    g = golden("agent")
+    heads = len(nvec)
+    acts = dev(g[f"{tag}_actions"].reshape(-1, heads), torch.int32)
+    mask = dev(g[f"{tag}_mask"]) if masked else None
+    a, lp, ent, val, logits = P.ops.policy_forward(dev(g[f"{tag}_params"]), O, 64, nvec, dev(g[f"{tag}_obs"]),
+                                                   mask=mask, actions=acts, want_logits=True)
+    close(logits, g[f"{tag}_logits"], rtol=1e-5, atol=1e-5)
+    close(val, g[f"{tag}_value"], rtol=1e-5, atol=1e-6)
+    close(lp, g[f"{tag}_logprob"], rtol=1e-5, atol=1e-5)
+    if masked:
+        close(ent, g[f"{tag}_entropy"], rtol=1e-5, atol=1e-5)
+    v2 = P.ops.value_forward(dev(g[f"{tag}_params"]), O, 64, nvec, dev(g[f"{tag}_obs"]))
+    assert torch.equal(v2, val)
+
+
+@pytest.mark.parametrize("H,n", [(64, 1), (64, 33), (64, 20000), (128, 777), (256, 4099)])
+def test_policy_forward_vs_oracle(P, orc, H, n):
+    rng = np.random.default_rng(H + n)
+    O, nvec = 4, [2]
+    params = P.orthogonal_init_params(O, H, nvec, seed=3)
+    params[params == 0] = rng.standard_normal((params == 0).sum()).astype(np.float32) * 0.1   # non-zero biases
+    obs = rng.standard_normal((n, O)).astype(np.float32)
+    u = rng.uniform(size=(n, 1)).astype(np.float32)
+    a, lp, ent, val, logits = P.ops.policy_forward(dev(params), O, H, nvec, dev(obs), uniforms=dev(u),
+                                                   want_logits=True)
+    ologits, oval = orc.mlp_forward(params, O, H, 2, obs)
+    close(logits, ologits, rtol=1e-5, atol=1e-6)
+    close(val, oval, rtol=1e-5, atol=2e-6)
+    oa, olp, _ = orc.categorical(logits.cpu().numpy(), nvec, uniforms=u)
+    assert np.array_equal(a.cpu().numpy(), oa)           # same logits, same uniforms -> same actions
+    close(lp, olp, rtol=1e-5, atol=2e-6)
+
+
+# ------------------------------------------------------------------------------------------------ GAE
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_gae_golden(P, golden, tag):
+    g = golden("gae")
+    adv, ret = P.ops.gae(dev(g[f"{tag}_rewards"]), dev(g[f"{tag}_values"]), dev(g[f"{tag}_dones"]),
+                         dev(g[f"{tag}_next_value"]), dev(g[f"{tag}_next_done"]), float(g["gamma"]), float(g["lam"]))
+    close(adv, g[f"{tag}_adv_gae1"], rtol=1e-5, atol=1e-6)
+    close(ret, g[f"{tag}_ret_gae1"], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("T,N", [(1, 1), (5, 3), (32, 8), (128, 4096), (17, 4098), (64, 65536 * 2 + 4),
+                                 (256, 65536)])
+@pytest.mark.parametrize("use_gae", [True, False])
+def test_gae_vs_oracle_bit_exact(P, orc, T, N, use_gae):
+    """same fp32 operation order as the oracle (no FMA contraction) => bit-identical, all vector widths"""
+    rng = np.random.default_rng(T * 7 + N)
+    r = np.where(rng.uniform(size=(T, N)) < 0.05, -1.0, 1.0).astype(np.float32)
+    v = rng.standard_normal((T, N)).astype(np.float32)
+    d = (rng.uniform(size=(T, N)) < 0.05).astype(np.float32)
+    nv = rng.standard_normal(N).astype(np.float32)
+    nd = (rng.uniform(size=N) < 0.05).astype(np.float32)
+    adv, ret = P.ops.gae(dev(r), dev(v), dev(d), dev(nv), dev(nd), 0.98, 0.95, use_gae)
+    oadv, oret = orc.gae(r, v, d, nv, nd, 0.98, 0.95, use_gae)
+    assert np.array_equal(adv.cpu().numpy(), oadv)
+    assert np.array_equal(ret.cpu().numpy(), oret)
+
+
+def test_gae_full_size_properties(P):
+    """config E per-GPU size [128, 131072] and config C [256, 65536]: size-independent properties.
+    (1) returns - advantages == values exactly as computed (ret = adv + V in fp32);
+    (2) an all-done rollout has adv = r - V (no bootstrap);  (3) linearity in (r, V, next_value)."""
+    for T, N in ((128, 131072), (256, 65536)):
+        gen = torch.Generator(device="cuda").manual_seed(T)
+        r = torch.randn(T, N, device="cuda", generator=gen)
+        v = torch.randn(T, N, device="cuda", generator=gen)
+        d = (torch.rand(T, N, device="cuda", generator=gen) < 0.05).float()
+        nv = torch.randn(N, device="cuda", generator=gen)
+        nd = torch.zeros(N, device="cuda")
+        adv, ret = P.ops.gae(r, v, d, nv, nd, 0.98, 0.95)
+        assert torch.equal(ret, adv + v)
+        ones = torch.ones_like(d)
+        adv1, _ = P.ops.gae(r, v, ones, nv, torch.ones(N, device="cuda"), 0.98, 0.95)
+        assert torch.equal(adv1, r - v)
+        adv2, _ = P.ops.gae(2 * r, 2 * v, d, 2 * nv, nd, 0.98, 0.95)
+        assert torch.equal(adv2, 2 * adv)          # scaling by 2 is exact in fp32
+
+
+# ---------------------------------------------------------------------------------------------- update
+def _run_update_case(P, orc, g, case):
+    O, K, nvec = int(g["O"]), int(g["K"]), [int(x) for x in g["nvec"]]
+    masked = bool(g["masked"])
+    params = g["params0"].copy()
+    for step in range(3):
+        p = f"s{step}_"
+        n = g[p + "obs"].shape[0]
+        mask = dev(g[p + "mask"]) if masked else None
+        stat = P.ops.adv_stats(dev(g[p + "adv"]), n, 1)
+        grads, diag = P.ops.update_minibatch(
+            dev(params), O, 64, nvec, dev(g[p + "obs"]), dev(g[p + "actions"], torch.int32),
+            dev(g[p + "old_logprob"]), dev(g[p + "adv"]), dev(g[p + "ret"]), dev(g[p + "old_val"]), 0, n,
+            mask=mask, adv_stat=stat, clip_coef=0.2, norm_adv=bool(g["norm_adv"]), clip_vloss=bool(g["clip_vloss"]),
+            ent_coef=float(g["ent_coef"]), vf_coef=0.5)
+        rd = g[p + "diag"]          # reference: {pg, v, ent, loss, kl, clipfrac, grad_norm, lr}
+        diag = diag.cpu().numpy()
+        close(diag[:2], rd[:2], rtol=2e-5, atol=1e-6)
+        close(diag[2], rd[2], rtol=2e-5, atol=1e-6)
+        close(diag[3:5], rd[3:5], rtol=2e-5, atol=2e-6)
+        assert diag[5] == rd[5]
+        rg = g[p + "grads"]
+        close(grads, rg, rtol=1e-4, atol=2e-6 * np.abs(rg).max())
+        # the oracle on the same inputs
+        og, od = orc.minibatch_grads(params, O, 64, np.array(nvec, np.int32), g[p + "obs"], g[p + "actions"],
+                                     g[p + "old_logprob"], g[p + "adv"], g[p + "ret"], g[p + "old_val"],
+                                     mask=g[p + "mask"] if masked else None, norm_adv=bool(g["norm_adv"]),
+                                     clip_vloss=bool(g["clip_vloss"]), ent_coef=float(g["ent_coef"]))
+        close(grads, og, rtol=1e-4, atol=2e-6 * np.abs(og).max())
+        # clip + AdamW from the reference's gradient and the moments so far
+        if step == 0:
+            m = torch.zeros(params.size, device="cuda")
+            v = torch.zeros(params.size, device="cuda")
+        dparams = dev(params)
+        norm = P.ops.clip_adamw(dparams, grads, m, v, float(g[p + "lr"]), step + 1, max_grad_norm=0.5)
+        close(norm, rd[6], rtol=1e-5)
+        close(dparams, g[p + "params_after"], rtol=1e-5, atol=1e-7)
+        params = g[p + "params_after"].copy()
+
+
+@pytest.mark.parametrize("case", ["discrete", "discrete_noclip", "masked", "multihead"])
+def test_minibatch_update_golden(P, orc, golden, case):
+    """loss terms, closed-form backward, grad-norm clip and AdamW against the compiled reference, 3 chained steps"""
+    _run_update_case(P, orc, golden("update_" + case), case)
+
+
+@pytest.mark.parametrize("H,O,nvec,n,masked,exact", [(64, 4, [2], 1000, False, False), (64, 4, [2], 5000, False, True),
+                                                     (128, 2, [3], 333, True, False),
+                                                     (256, 2, [3, 3, 3, 3, 3, 2, 2, 2], 777, True, False),
+                                                     (64, 4, [1], 65, False, False)])
+def test_update_vs_oracle_permuted(P, orc, H, O, nvec, n, masked, exact):
+    """gather through a permutation, ragged tile counts, all hidden widths, masked multi-head, exact entropy"""
+    rng = np.random.default_rng(H + n)
+    K, heads = sum(nvec), len(nvec)
+    batch = n * 3 + 7
+    params = P.orthogonal_init_params(O, H, nvec, seed=5)
+    params += rng.standard_normal(params.size).astype(np.float32) * 0.02
+    obs = rng.standard_normal((batch, O)).astype(np.float32)
+    mask = None
+    if masked:
+        mask = (rng.uniform(size=(batch, K)) < 0.7).astype(np.uint8)
+        off = 0
+        for k in nvec:
+            mask[:, off] = 1
+            off += k
+    u = rng.uniform(size=(batch, heads)).astype(np.float32)
+    logits, val = orc.mlp_forward(params, O, H, K, obs)
+    acts, lp, _ = orc.categorical(logits, nvec, mask=mask, uniforms=u)
+    old_lp = (lp + rng.standard_normal(batch).astype(np.float32) * 0.3).astype(np.float32)   # exercise clipping
+    old_val = (val + rng.standard_normal(batch).astype(np.float32) * 0.3).astype(np.float32)
+    adv = rng.standard_normal(batch).astype(np.float32) * 2 + 0.5
+    ret = (val + rng.standard_normal(batch).astype(np.float32)).astype(np.float32)
+    perm = rng.permutation(batch).astype(np.int32)
+    start = 5
+    rows = perm[start:start + n]
+    mode = P.ENTROPY_EXACT if exact else P.ENTROPY_REFERENCE
+    dperm = dev(perm)
+    # stats over the minibatch rows: use mb_size=n on a shifted view of the permutation
+    stat = P.ops.adv_stats(dev(adv), n, 1, perm=dperm[start:start + n].contiguous())
+    grads, diag = P.ops.update_minibatch(dev(params), O, H, nvec, dev(obs), dev(acts), dev(old_lp), dev(adv),
+                                         dev(ret), dev(old_val), start, n, perm=dperm,
+                                         mask=None if mask is None else dev(mask), adv_stat=stat, ent_coef=0.01,
+                                         entropy_mode=mode)
+    og, od = orc.minibatch_grads(params, O, H, np.array(nvec, np.int32), obs[rows], acts[rows], old_lp[rows],
+                                 adv[rows], ret[rows], old_val[rows], mask=None if mask is None else mask[rows],
+                                 ent_coef=0.01, entropy_mode=mode)
+    close(stat.cpu().numpy()[0], od[6:8], rtol=1e-6)
+    close(diag.cpu().numpy()[:6], od[:6], rtol=5e-5, atol=2e-6)
+    close(grads, og, rtol=1e-4, atol=3e-6 * np.abs(og).max())
+    assert od[5] > 0.05           # the clip branch was exercised
+    # run-to-run determinism (no atomics in the gradient reduction)
+    grads2, _ = P.ops.update_minibatch(dev(params), O, H, nvec, dev(obs), dev(acts), dev(old_lp), dev(adv),
+                                       dev(ret), dev(old_val), start, n, perm=dperm,
+                                       mask=None if mask is None else dev(mask), adv_stat=stat, ent_coef=0.01,
+                                       entropy_mode=mode)
+    assert torch.equal(grads, grads2)
+
+
+def test_adv_partials_merge(P):
+    """data-parallel merge: partial moments of two shards, summed, finalise to the stats of the union"""
+    gen = torch.Generator(device="cuda").manual_seed(0)
+    a = torch.randn(8192, device="cuda", generator=gen) * 3 + 1
+    p0 = P.ops.adv_partials(a[:4096].contiguous(), 1024, 4)
+    p1 = P.ops.adv_partials(a[4096:].contiguous(), 1024, 4)
+    st = P.ops.adv_stats_finalize(p0 + p1).cpu().numpy()
+    for mb in range(4):
+        x = torch.cat([a[mb * 1024:(mb + 1) * 1024], a[4096 + mb * 1024:4096 + (mb + 1) * 1024]]).double()
+        close(st[mb], [x.mean().item(), x.std(unbiased=True).item()], rtol=1e-6)
+
+
+def test_explained_variance(P, orc):
+    rng = np.random.default_rng(0)
+    for n in (2, 1000, 524288):
+        r = rng.standard_normal(n).astype(np.float32) * 3 + 10
+        v = (r * 0.7 + rng.standard_normal(n) * 0.2).astype(np.float32)
+        ev = P.ops.explained_variance(dev(r), dev(v)).item()
+        assert abs(ev - orc.explained_variance(r, v)) < 2e-5
+        ev2 = P.ops.explained_variance(dev(r), dev(v)).item()     # workspace left clean
+        assert ev == ev2
+
+
+@pytest.mark.parametrize("batch", [1, 2, 255, 256, 4097, 524288, 16777216])
+def test_permutation_is_bijection(P, batch):
+    p = P.ops.make_permutation(batch, 7, 3)
+    assert p.min().item() == 0 and p.max().item() == batch - 1
+    assert torch.equal(torch.sort(p.long()).values, torch.arange(batch, device="cuda"))
+    if batch > 256:
+        q = P.ops.make_permutation(batch, 7, 4)
+        assert (p == q).float().mean().item() < 0.01      # a different epoch gives a different shuffle
+        assert (p.long() == torch.arange(batch, device="cuda")).float().mean().item() < 0.01
+
+
+# ---------------------------------------------------------------------------------------------- rollout
+@pytest.mark.parametrize("kind,O,nvec,masked,H,n,T", [(0, 4, [2], False, 64, 100, 24), (0, 4, [1], False, 64, 8, 32),
+                                                      (1, 2, [3], True, 64, 77, 20), (1, 2, [3], False, 256, 40, 6),
+                                                      (0, 4, [2], False, 128, 4096, 8)])
+def test_fused_rollout_vs_oracle(P, orc, kind, O, nvec, masked, H, n, T):
+    """Every step of the fused rollout is checked from the GPU's own previous observation (single-step
+    comparisons, so CartPole's chaos cannot amplify ulp differences): forward -> sample on the same Philox
+    uniform -> env transition with truncation/auto-reset -> stored rollout rows; then bootstrap + GAE."""
+    from philox_np import reset_uniforms, sample_uniforms
+    seed, counter, base, max_ep = 4242, 1000, 64, 9
+    K, heads = sum(nvec), len(nvec)
+    params = P.orthogonal_init_params(O, H, nvec, seed=11)
+    params[-K:] = np.linspace(-0.3, 0.3, K)                      # non-uniform policy
+    u0 = np.random.default_rng(1).uniform(size=(n, 4)).astype(np.float32)
+    state, ep_len, ep_ret, obs0 = P.ops.env_reset(kind, n, uniforms=dev(u0))
+    next_done = torch.zeros(n, device="cuda")
+    st0 = state.cpu().numpy().T.copy()
+    out = P.ops.rollout(dev(params), O, H, nvec, kind, state, ep_len, ep_ret, next_done, T, max_ep, 0.98, 0.95,
+                        masked=masked, seed=seed, counter=counter, env_id_base=base)
+    o = {k: (v.cpu().numpy() if v is not None else None) for k, v in out.items()}
+    assert np.array_equal(o["obs"][0], st0)
+    o_len = np.zeros(n, np.int32)
+    o_ret = np.zeros(n, np.float32)
+    prev_done = np.zeros(n, np.float32)
+    n_fin, sum_len, sum_ret = 0, 0.0, 0.0
+    ids = np.arange(n) + base
+    for t in range(T):
+        obs_t = o["obs"][t]
+        assert np.array_equal(o["dones"][t], prev_done)           # m_dones[t] = flag entering the step
+        logits, val = orc.mlp_forward(params, O, H, K, obs_t)
+        close(o["values"][t], val, rtol=1e-5, atol=2e-6)
+        u = sample_uniforms(seed, ids, counter + t, heads)
+        mask = np.ones((n, K), np.uint8) if masked else None
+        oa, olp, _ = orc.categorical(logits, nvec, mask=mask, uniforms=u)
+        # logits differ by ~1e-7 between the FMA kernel and the oracle: allow the epsilon band
+        _, _, _, pr, _ = orc.categorical(logits, nvec, mask=mask, uniforms=u, want_probs=True)
+        edge = np.min(np.abs(np.cumsum(pr[:, :nvec[0]].astype(np.float64), 1) - u[:, :1]), 1) < 2.0 ** -20
+        ga = o["actions"][t]
+        assert np.all((ga == oa).all(1) | edge)
+        _, olp2, _ = orc.categorical(logits, nvec, mask=mask, actions=ga)
+        close(o["logprobs"][t], olp2, rtol=1e-5, atol=2e-6)
+        if masked:
+            assert np.all(o["masks"][t] == 1)
+        ru = reset_uniforms(seed, ids, counter + t)
+        st = obs_t.copy()
+        oobs, orew, odone, ofl, ofr = orc.env_step(kind, st, o_len, o_ret, ga[:, 0].astype(np.int32), max_ep, ru)
+        assert np.array_equal(o["rewards"][t], orew)
+        nxt = o["obs"][t + 1] if t + 1 < T else state.cpu().numpy().T
+        close(nxt, oobs, rtol=1e-6, atol=1e-7)
+        prev_done = odone
+        n_fin += int((ofl > 0).sum()); sum_len += float(ofl.sum()); sum_ret += float(ofr.sum())
+    assert np.array_equal(next_done.cpu().numpy(), prev_done)
+    assert np.array_equal(ep_len.cpu().numpy(), o_len)
+    assert n_fin > 0
+    close(o["ep_stats"], [n_fin, sum_len, sum_ret], rtol=1e-12)
+    # bootstrap + GAE on the stored rows: bit-exact against the oracle given the GPU's values
+    _, nval = orc.mlp_forward(params, O, H, K, state.cpu().numpy().T.copy())
+    close(o["next_value"], nval, rtol=1e-5, atol=2e-6)
+    oadv, oret = orc.gae(o["rewards"], o["values"], o["dones"], o["next_value"], prev_done, 0.98, 0.95)
+    assert np.array_equal(o["adv"], oadv) and np.array_equal(o["ret"], oret)
+
+
+# ---------------------------------------------------------------------------------------------- trainer
+def test_trainer_iteration_matches_composed_oracle(P, orc):
+    """One full PPO iteration of the C++ trainer (config A sizes, K=2) replayed minibatch by minibatch with the
+    oracle from the trainer's own rollout buffers and permutation."""
+    N, T, MB, E = 8, 32, 4, 2
+    tr = P.Trainer(num_envs=N, num_steps=T, num_minibatches=MB, update_epochs=E, nvec=(2,), seed=2)
+    p0 = tr.get_params()
+    lr = 1e-3
+    tr.rollout(lr)
+    torch.cuda.synchronize()
+    B, mb = N * T, N * T // MB
+    bufs = {k: tr.buffer(k).cpu().numpy().copy() for k in ("obs", "actions", "logprobs", "adv", "ret", "values")}
+    obs = bufs["obs"].reshape(B, 4)
+    params = p0.copy()
+    m = np.zeros_like(params); v = np.zeros_like(params)
+    step = 0
+    for e in range(E):
+        tr.begin_epoch(e)
+        torch.cuda.synchronize()
+        perm = tr.buffer("perm").cpu().numpy().copy()
+        assert sorted(perm.tolist()) == list(range(B))
+        for k in range(MB):
+            tr.minibatch_grads(k)
+            tr.apply()
+            rows = perm[k * mb:(k + 1) * mb]
+            og, od = orc.minibatch_grads(params, 4, 64, np.array([2], np.int32), obs[rows],
+                                         bufs["actions"].reshape(B, 1)[rows], bufs["logprobs"][rows],
+                                         bufs["adv"][rows], bufs["ret"][rows], bufs["values"][rows])
+            step += 1
+            orc.clip_adamw(params, og, m, v, lr, step)
+            torch.cuda.synchronize()
+            close(tr.get_params(), params, rtol=2e-4, atol=2e-6)
+    res = tr.finish(lr)
+    close(res["pg_loss"], od[0], rtol=1e-3, atol=1e-5)
+    close(res["v_loss"], od[1], rtol=1e-3, atol=1e-5)
+    close(res["approx_kl"], od[4], rtol=1e-2, atol=1e-6)
+    ev = orc.explained_variance(bufs["ret"], bufs["values"])
+    assert abs(res["explained_variance"] - ev) < 1e-4
+    tr.close()
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_trainer_learns_cartpole(P, graph):
+    """Learning-curve acceptance: CartPole, action_size=2, shipped hyper-parameters at 64 envs:
+    mean episode length must rise well above the random-policy ~20 within 60 iterations."""
+    tr = P.Trainer(num_envs=64, num_steps=32, num_minibatches=4, update_epochs=10, nvec=(2,), seed=2,
+                   use_cuda_graph=graph)
+    iters, lr0 = 60, 1e-3
+    first, last = None, None
+    for it in range(iters):
+        lr = (1.0 - it / iters) * lr0                       # anneal_lr (:514-518)
+        r = tr.iterate(lr)
+        assert np.isfinite(r["loss"]) and np.isfinite(r["grad_norm"])
+        if r["episodes"] > 0:
+            ml = r["ep_len_sum"] / r["episodes"]
+            first = ml if first is None else first
+            last = ml
+    assert first < 40
+    assert last > 100, f"mean episode length only reached {last}"
+    tr.close()
+
+
+def test_trainer_graph_equals_eager(P):
+    """the captured-graph iteration is the same arithmetic as the eager launches: identical parameters"""
+    out = []
+    for graph in (False, True):
+        tr = P.Trainer(num_envs=32, num_steps=16, num_minibatches=2, update_epochs=3, nvec=(2,), seed=5,
+                       use_cuda_graph=graph)
+        for it in range(4):
+            tr.iterate(1e-3 * (1 - it / 4))
+        out.append(tr.get_params())
+        tr.close()
+    assert np.array_equal(out[0], out[1])
