@@ -22,12 +22,19 @@ constexpr int WS_LD = 68;  // Ws[64][68]
 __host__ __device__ constexpr int lda_of(int H) { return H + 4; }
 
 __device__ inline float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+// 4 consecutive floats from global memory through the read-only path.  The flat parameter slab keeps the
+// reference's order (PPO/Agent.cpp:41-66), in which the critic's 1-element output bias leaves every actor
+// tensor off 16 B alignment, so the vector load is only taken when the address allows it.
+__device__ inline float4 ldg4_any(const float* p) {
+    if ((reinterpret_cast<uintptr_t>(p) & 15u) == 0) return __ldg(reinterpret_cast<const float4*>(p));
+    return make_float4(__ldg(p), __ldg(p + 1), __ldg(p + 2), __ldg(p + 3));
+}
 
 // Stage W[n0:n0+64, k0:k0+64] (row-major, leading dim ldw) into Ws[64][WS_LD]; coalesced along k.
 __device__ inline void stage_w(float* Ws, const float* __restrict__ W, int ldw, int n0, int k0) {
     for (int e = threadIdx.x; e < 64 * 16; e += MLP_THREADS) {
         const int r = e >> 4, c4 = (e & 15) * 4;
-        const float4 v = __ldg(reinterpret_cast<const float4*>(W + (size_t)(n0 + r) * ldw + k0 + c4));
+        const float4 v = ldg4_any(W + (size_t)(n0 + r) * ldw + k0 + c4);
         *reinterpret_cast<float4*>(Ws + r * WS_LD + c4) = v;
     }
 }
@@ -107,7 +114,7 @@ __device__ inline void layer3_fwd(const float* Hin, const float* __restrict__ W3
         float acc = 0.0f;
         for (int k = part * 4; k < H; k += 16) {
             const float4 a = ld4(Hin + m * LDA + k);
-            const float4 w = __ldg(reinterpret_cast<const float4*>(W3 + q * H + k));
+            const float4 w = ldg4_any(W3 + q * H + k);
             acc = fmaf(a.x, w.x, acc); acc = fmaf(a.y, w.y, acc);
             acc = fmaf(a.z, w.z, acc); acc = fmaf(a.w, w.w, acc);
         }
@@ -176,12 +183,18 @@ __device__ inline void layer2_bwd_dw(const float* dZ2, const float* H1, float* _
                     acc[i][3] = fmaf(dd[i], a.w, acc[i][3]);
                 }
             }
+            const bool al = (reinterpret_cast<uintptr_t>(gW2) & 15u) == 0;  // actor slabs sit 1 float off (see ldg4_any)
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                float4* p = reinterpret_cast<float4*>(gW2 + (size_t)(n0 + gn * 4 + i) * H + k0 + gk * 4);
-                float4 v = *p;
-                v.x += acc[i][0]; v.y += acc[i][1]; v.z += acc[i][2]; v.w += acc[i][3];
-                *p = v;
+                float* q = gW2 + (size_t)(n0 + gn * 4 + i) * H + k0 + gk * 4;
+                if (al) {
+                    float4* p = reinterpret_cast<float4*>(q);
+                    float4 v = *p;
+                    v.x += acc[i][0]; v.y += acc[i][1]; v.z += acc[i][2]; v.w += acc[i][3];
+                    *p = v;
+                } else {
+                    q[0] += acc[i][0]; q[1] += acc[i][1]; q[2] += acc[i][2]; q[3] += acc[i][3];
+                }
             }
         }
     for (int n = threadIdx.x; n < H; n += MLP_THREADS) {

@@ -67,6 +67,7 @@ class Trainer:
             raise capi.PpoError("ppo_trainer_create: " + capi.last_error())
         self.h = C.c_void_p(self.h)
         self.comm = None
+        self._side = None
         self.n_params = int(load().ppo_num_params(C.byref(c.dims)))
         self.set_params(orthogonal_init_params(obs_dim, hidden, nvec, init_seed))
         self.reset_envs()
@@ -130,7 +131,26 @@ class Trainer:
         check(load().ppo_trainer_set_comm(self.h, self.comm))
 
     # -- one PPO iteration (train() loop body)
+    def _graph_stream(self, stream):
+        """stream capture cannot run on the legacy default stream: route graph replay through a side stream
+        that is ordered after / before the caller's current stream"""
+        cur = stream if stream is not None else torch.cuda.current_stream()
+        if not self.cfg.use_cuda_graph or cur.cuda_stream != 0:
+            return cur, None
+        if self._side is None:
+            self._side = torch.cuda.Stream()
+        self._side.wait_stream(cur)
+        return self._side, cur
+
     def iterate(self, lr, want_result=True, stream=None):
+        stream, back = self._graph_stream(stream)
+        try:
+            return self._iterate(lr, want_result, stream)
+        finally:
+            if back is not None:
+                back.wait_stream(stream)
+
+    def _iterate(self, lr, want_result, stream):
         if want_result:
             r = IterResult()
             check(load().ppo_trainer_iterate(self.h, lr, C.byref(r), stream_ptr(stream)))
