@@ -285,6 +285,14 @@ int ppo_comm_allreduce_f32(ppo_comm* c, float* buf, int64_t count, ppo_stream_t 
 int ppo_comm_allreduce_f64(ppo_comm* c, double* buf, int64_t count, ppo_stream_t stream);
 int ppo_trainer_set_comm(ppo_trainer* t, ppo_comm* comm);
 
+/* ---- diagnostics ----------------------------------------------------------------------------- */
+/* Known-answer probe of the tcgen05 (16-bit operands, fp32 TMEM accumulator) building blocks the fused kernels
+ * use (csrc/umma.cuh).  One 128-thread CTA, one GEMM with operands rounded to fp16 (fmt 0) or bf16 (fmt 1):
+ * mode 0: D[128,64] = A[128,64] B[64,64]^T; 1: D = A B[64,64]; 2: D[64,64] = A^T B[128,64]; 3: D[64,16] = A^T B[128,16].
+ * D receives the raw tensor-memory image [128 lanes][64 columns] (M = 64 results sit in lanes
+ * (m % 16) + 32 (m / 16)).  No reference counterpart. */
+int ppo_debug_umma_probe(int mode, int fmt, const float* A, const float* B, float* D, ppo_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
