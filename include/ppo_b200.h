@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PPO_B200_ABI_VERSION 1
+#define PPO_B200_ABI_VERSION 2
 #define PPO_MAX_HEADS 8
 #define PPO_MAX_LOGITS 64
 
@@ -61,6 +61,17 @@ typedef struct {
     float vf_coef;        /* m_vf_coef        */
     int32_t entropy_mode; /* PPO_ENTROPY_*    */
 } ppo_hyper;
+
+/* Arithmetic of the MLP GEMMs in the fused update kernel (K5).  The reference's switch for this is
+ * at::globalContext().setAllowTF32CuBLAS(true) (PPO/PPO_Discrete.cpp:56): reduced-precision tensor-core operands with
+ * fp32 accumulation on CUDA, plain fp32 on CPU.  PPO_MATH_FP16 (default; 11 significant bits like TF32, conversions saturate) / PPO_MATH_BF16: tcgen05 tensor cores,
+ * 16-bit operands, fp32 accumulate, master weights / activations' non-GEMM math / Adam in fp32; PPO_MATH_FP32: fp32 FMA
+ * kernels (the parity mode: matches the oracle to 1e-4).  Shapes outside the tensor-core kernel's envelope
+ * (hidden != 64, obs_dim > 7, sum of logits > 32) use the FMA kernels in every mode.  Process-wide, like the
+ * reference's; a captured CUDA graph keeps the mode it was captured with. */
+enum { PPO_MATH_FP32 = 0, PPO_MATH_BF16 = 1, PPO_MATH_FP16 = 2 };
+int ppo_set_math_mode(int mode);
+int ppo_get_math_mode(void);
 
 const char* ppo_last_error(void);
 int ppo_abi_version(void);

@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libppo_b200.so")
 PPO_MAX_HEADS = 8
 ENV_CARTPOLE, ENV_MOUNTAINCAR = 0, 1
 ENTROPY_REFERENCE, ENTROPY_EXACT = 0, 1
+MATH_FP32, MATH_BF16, MATH_FP16 = 0, 1, 2
 
 
 class PpoError(RuntimeError):
@@ -70,6 +71,8 @@ _PROTOS = {
     # name: (restype, argtypes)
     "ppo_last_error": (C.c_char_p, []),
     "ppo_abi_version": (C.c_int, []),
+    "ppo_set_math_mode": (C.c_int, [C.c_int]),
+    "ppo_get_math_mode": (C.c_int, []),
     "ppo_device_count": (C.c_int, []),
     "ppo_device_info": (C.c_int, [C.POINTER(C.c_int)] * 3),
     "ppo_num_params": (C.c_int64, [C.POINTER(Dims)]),

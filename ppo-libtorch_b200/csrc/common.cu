@@ -19,6 +19,9 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
     return PPO_ERR_CUDA;
 }
 
+static int g_math_mode = PPO_MATH_FP16;
+int math_mode() { return g_math_mode; }
+
 int sm_count() {
     static int cached_dev = -1, cached = 0;
     int dev = 0;
@@ -64,6 +67,12 @@ using namespace ppo;
 
 extern "C" const char* ppo_last_error(void) { return g_err; }
 extern "C" int ppo_abi_version(void) { return PPO_B200_ABI_VERSION; }
+extern "C" int ppo_get_math_mode(void) { return g_math_mode; }
+extern "C" int ppo_set_math_mode(int mode) {
+    PPO_REQUIRE(mode == PPO_MATH_FP32 || mode == PPO_MATH_BF16 || mode == PPO_MATH_FP16, "ppo_set_math_mode: mode=%d", mode);
+    g_math_mode = mode;
+    return PPO_OK;
+}
 
 extern "C" int ppo_device_count(void) {
     int n = 0;

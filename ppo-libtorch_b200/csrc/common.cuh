@@ -28,6 +28,7 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
         }                                       \
     } while (0)
 
+int math_mode();  // PPO_MATH_* selected with ppo_set_math_mode
 int sm_count();  // cached multiprocessor count of the current device (0 if no device)
 
 // ---------------------------------------------------------------- dims helpers

@@ -153,7 +153,7 @@ template <int FMT>
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
     uint32_t r;
     if constexpr (FMT == FMT_BF16) asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-    else asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    else asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));  // saturate, never inf
     return r;
 }
 template <int FMT>

@@ -10,33 +10,10 @@
 // Weight-gradient partials accumulate in a per-CTA slab of `workspace`; reduce_kernel sums the
 // slabs in CTA order (no atomics: results are run-to-run identical) and finishes the diagnostics.
 #include "policy.cuh"
+#include "ppo_loss.cuh"
+#include "update.cuh"
 
 namespace ppo {
-
-constexpr int UPD_MAX_GRID = 296;  // 2 CTAs x 148 SMs
-constexpr int UPD_NDIAG = 8;       // pg, v, ent, kl, clip (+3 spare) partial sums per CTA
-
-__host__ __device__ inline int64_t slab_stride(int P) { return ((int64_t)P + 31) & ~(int64_t)31; }
-
-struct UpdArgs {
-    const float* params;
-    Dims d;
-    const float* obs;
-    const uint8_t* mask;
-    const int32_t* actions;
-    const float* old_logprob;
-    const float* adv;
-    const float* ret;
-    const float* old_val;
-    const int32_t* perm;
-    int64_t mb_start;
-    int mb_size;
-    float inv_n;
-    const float* adv_stats;  // {mean, std} or nullptr
-    ppo_hyper hp;
-    float* slabs;    // [grid][slab_stride(P)]
-    double* dpart;   // [grid][UPD_NDIAG]
-};
 
 template <int TM, int H>
 __device__ inline void net_backward(float* sm, const TileLayout& L, int O, const float* __restrict__ params,
@@ -65,10 +42,9 @@ __global__ void __launch_bounds__(MLP_THREADS) update_kernel(const UpdArgs a) {
     for (int i = threadIdx.x; i < P; i += MLP_THREADS) g[i] = 0.0f;
 
     const bool masked = a.mask != nullptr;
-    const float c = a.hp.clip_coef, lo = 1.0f - c, hi = 1.0f + c;
     float meanf = 0.0f, stdf = 1.0f;
     if (a.hp.norm_adv) { meanf = a.adv_stats[0]; stdf = a.adv_stats[1]; }
-    double s_pg = 0.0, s_v = 0.0, s_ent = 0.0, s_kl = 0.0, s_clip = 0.0;
+    RowSums rs;
 
     const int ntiles = (a.mb_size + TM - 1) / TM;
     const int t = threadIdx.x;
@@ -95,58 +71,8 @@ __global__ void __launch_bounds__(MLP_THREADS) update_kernel(const UpdArgs a) {
             if (t < rows) {
                 const int64_t r = sidx[t];
                 const uint64_t mbits = masked ? pack_mask(a.mask + r * K, K) : ~0ull;
-                const int32_t* act = a.actions + r * heads;
-                // pass 1: log-prob of the stored actions + entropy, summed over heads (Agent.cpp:168)
-                float newlogp = 0.0f, ent = 0.0f;
-                float hent[PPO_MAX_HEADS];
-                HeadStats hs[PPO_MAX_HEADS];
-                int off = 0;
-                for (int h = 0; h < heads; h++) {
-                    const int Kh = a.d.nvec[h];
-                    const uint64_t mb = mbits >> off;
-                    hs[h] = head_stats(x + off, Kh, mb, masked);
-                    const int aa = act[h];
-                    newlogp = __fadd_rn(newlogp,
-                                        head_logp(masked_logit(x[off + aa], !masked || ((mb >> aa) & 1ull)), hs[h]));
-                    hent[h] = head_entropy(x + off, Kh, mb, masked, hs[h], a.hp.entropy_mode);
-                    ent = __fadd_rn(ent, hent[h]);
-                    off += Kh;
-                }
-                const float logratio = newlogp - __ldg(a.old_logprob + r);  // :585
-                const float ratio = expf(logratio);                         // :586
-                s_kl += (double)((ratio - 1.0f) - logratio);                // :352
-                if (fabsf(ratio - 1.0f) > c) s_clip += 1.0;                 // :348
-                float A = __ldg(a.adv + r);
-                if (a.hp.norm_adv) A = __fdiv_rn(A - meanf, stdf + 1e-8f);  // :591-594
-                const float rc = ratio < lo ? lo : (ratio > hi ? hi : ratio);
-                const float pg1 = -A * ratio, pg2 = -A * rc;                // :597-598
-                s_pg += (double)(pg1 > pg2 ? pg1 : pg2);
-                s_ent += (double)ent;
-                // d pg / d ratio: ATen max splits ties 1/2-1/2, clamp's mask is inclusive (SURVEY §8 a-bis)
-                float dpg_dr;
-                if (ratio >= lo && ratio <= hi) dpg_dr = -A;
-                else if (pg1 > pg2) dpg_dr = -A;
-                else if (pg1 == pg2) dpg_dr = -0.5f * A;
-                else dpg_dr = 0.0f;
-                const float g_logp = a.inv_n * dpg_dr * ratio;
-                const bool exact = masked || a.hp.entropy_mode == PPO_ENTROPY_EXACT;
-                const float ge = a.hp.ent_coef * a.inv_n;
-                off = 0;
-                for (int h = 0; h < heads; h++) {
-                    const int Kh = a.d.nvec[h];
-                    const uint64_t mb = mbits >> off;
-                    const int aa = act[h];
-                    for (int j = 0; j < Kh; j++) {
-                        const bool valid = !masked || ((mb >> j) & 1ull);
-                        const float xm = masked_logit(x[off + j], valid);
-                        const float p = head_prob(xm, hs[h]);
-                        float dz = g_logp * ((j == aa ? 1.0f : 0.0f) - p);
-                        if (exact && ge != 0.0f && p > 0.0f) dz += ge * p * (head_logp(xm, hs[h]) + hent[h]);
-                        if (!valid) dz = 0.0f;
-                        x[off + j] = dz;
-                    }
-                    off += Kh;
-                }
+                actor_row_loss(x, a.d, masked, mbits, a.actions + r * heads, __ldg(a.old_logprob + r), __ldg(a.adv + r),
+                               a.hp, meanf, stdf, a.inv_n, rs);
             } else {
                 for (int j = 0; j < K; j++) x[j] = 0.0f;
             }
@@ -160,25 +86,8 @@ __global__ void __launch_bounds__(MLP_THREADS) update_kernel(const UpdArgs a) {
             float gv = 0.0f;
             if (t < rows) {
                 const int64_t r = sidx[t];
-                const float value = sm[L.vs + t];
-                const float R = __ldg(a.ret + r);
-                const float du = value - R;
-                const float u = du * du;
-                float dv;
-                if (a.hp.clip_vloss) {  // :603-618
-                    const float vo = __ldg(a.old_val + r);
-                    const float dvo = value - vo;
-                    const float dcl = dvo < -c ? -c : (dvo > c ? c : dvo);
-                    const float vc = vo + dcl;
-                    const float w = (vc - R) * (vc - R);
-                    s_v += (double)(u > w ? u : w);
-                    const float dw = (dvo >= -c && dvo <= c) ? (vc - R) : 0.0f;
-                    dv = (u > w) ? du : ((w > u) ? dw : 0.5f * du + 0.5f * dw);
-                } else {  // :621-625
-                    s_v += (double)u;
-                    dv = du;
-                }
-                gv = a.hp.vf_coef * a.inv_n * dv;
+                gv = critic_row_loss(sm[L.vs + t], __ldg(a.ret + r), a.hp.clip_vloss ? __ldg(a.old_val + r) : 0.0f, a.hp,
+                                     a.inv_n, rs);
             }
             sm[L.vs + t] = gv;
         }
@@ -190,8 +99,8 @@ __global__ void __launch_bounds__(MLP_THREADS) update_kernel(const UpdArgs a) {
     __syncthreads();
     double* red = reinterpret_cast<double*>(sm);  // reuse: 5 x TM doubles
     if (t < TM) {
-        red[0 * TM + t] = s_pg; red[1 * TM + t] = s_v; red[2 * TM + t] = s_ent;
-        red[3 * TM + t] = s_kl; red[4 * TM + t] = s_clip;
+        red[0 * TM + t] = rs.pg; red[1 * TM + t] = rs.v; red[2 * TM + t] = rs.ent;
+        red[3 * TM + t] = rs.kl; red[4 * TM + t] = rs.clip;
     }
     __syncthreads();
     if (t < 5) {
@@ -286,6 +195,18 @@ extern "C" int ppo_update_minibatch(const float* params, const ppo_dims* dims, c
     a.dpart = reinterpret_cast<double*>(reinterpret_cast<char*>(workspace) +
                                         (size_t)UPD_MAX_GRID * slab_stride(P) * sizeof(float));
     cudaStream_t st = as_stream(stream);
+    const int mode = math_mode();
+    if (mode != PPO_MATH_FP32) {  // tensor-core path when the shape fits its envelope, else the FMA kernels below
+        int grid = 0;
+        const int rc = launch_update_tc(a, mode == PPO_MATH_BF16 ? 1 : 0, &grid, st);
+        if (rc == PPO_OK) {
+            reduce_kernel<<<(P + 255) / 256, 256, 0, st>>>(a.slabs, a.dpart, grid, P, slab_stride(P), a.inv_n,
+                                                           a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out);
+            PPO_LAUNCH_CHECK();
+            return PPO_OK;
+        }
+        if (rc != PPO_ERR_UNSUPPORTED) return rc;
+    }
     switch (a.d.H) {
         case 64: return launch_update<64, 64>(a, grads_out, diag_out, st);
         case 128: return launch_update<32, 128>(a, grads_out, diag_out, st);

@@ -27,6 +27,16 @@ def num_params(obs_dim, hidden, nvec):
     return int(n)
 
 
+def set_math_mode(mode):
+    """capi.MATH_FP32 (FMA kernels, oracle-exact to 1e-4) / MATH_BF16 (default) / MATH_FP16 (tcgen05 tensor cores);
+    the reference's counterpart is at::globalContext().setAllowTF32CuBLAS (PPO/PPO_Discrete.cpp:56)."""
+    check(load().ppo_set_math_mode(int(mode)))
+
+
+def get_math_mode():
+    return int(load().ppo_get_math_mode())
+
+
 # ---- envs (K3) ------------------------------------------------------------------------------------
 def env_reset(kind, n, uniforms=None, seed=0, counter=0, device="cuda"):
     """PPO_Discrete::initEnvs.  Returns (state_soa [S,n], ep_len i32 [n], ep_ret [n], obs [n,S])."""

@@ -20,6 +20,16 @@ def P():
     return p
 
 
+@pytest.fixture(autouse=True)
+def fp32_math(P):
+    """this module states fp32 tolerances: run the update on the FMA kernels (tests/test_gpu_tensorcore.py covers the
+    tensor-core modes with their own tolerance)"""
+    prev = P.ops.get_math_mode()
+    P.ops.set_math_mode(P.capi.MATH_FP32)
+    yield
+    P.ops.set_math_mode(prev)
+
+
 def dev(a, dtype=None):
     t = torch.from_numpy(np.ascontiguousarray(a))
     if dtype is not None:
