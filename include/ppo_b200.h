@@ -167,9 +167,12 @@ int ppo_rollout(const float* params, const ppo_dims* dims, const ppo_rollout_cfg
  * consecutive minibatches of `mb_size` rows of one epoch.  perm (int32 [batch]) NULL =>
  * identity.  stats_out [n_mb,2] = {mean, std}.  partial_out != NULL => also (or only, if
  * stats_out == NULL) write raw double partials [n_mb,3] = {count, sum, sum of squares} for a
- * data-parallel allreduce; ppo_adv_stats_finalize turns (reduced) partials into stats. */
+ * data-parallel allreduce; ppo_adv_stats_finalize turns (reduced) partials into stats.
+ * workspace: optional scratch of ppo_adv_stats_workspace_bytes(n_mb) bytes, zeroed once by the caller (left zeroed);
+ * with it, large minibatches are reduced by 32 CTAs each (raw moments in double) instead of one. */
+int64_t ppo_adv_stats_workspace_bytes(int n_mb);
 int ppo_adv_stats(const float* adv, const int32_t* perm, int64_t batch, int mb_size, int n_mb,
-                  float* stats_out, double* partial_out, ppo_stream_t stream);
+                  float* stats_out, double* partial_out, void* workspace, ppo_stream_t stream);
 int ppo_adv_stats_finalize(const double* partial, int n_mb, float* stats_out, ppo_stream_t stream);
 /* Scratch the update kernel needs: returns bytes for `workspace`. */
 int64_t ppo_update_workspace_bytes(const ppo_dims* dims);

@@ -88,7 +88,8 @@ _PROTOS = {
     "ppo_value_forward": (C.c_int, [_P, C.POINTER(Dims), C.c_int, _P, _P, _P]),
     "ppo_gae": (C.c_int, [C.c_int, C.c_int, _P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_int, _P, _P, _P]),
     "ppo_rollout": (C.c_int, [_P, C.POINTER(Dims), C.POINTER(RolloutCfg)] + [_P] * 16),
-    "ppo_adv_stats": (C.c_int, [_P, _P, C.c_int64, C.c_int, C.c_int, _P, _P, _P]),
+    "ppo_adv_stats_workspace_bytes": (C.c_int64, [C.c_int]),
+    "ppo_adv_stats": (C.c_int, [_P, _P, C.c_int64, C.c_int, C.c_int, _P, _P, _P, _P]),
     "ppo_adv_stats_finalize": (C.c_int, [_P, C.c_int, _P, _P]),
     "ppo_update_workspace_bytes": (C.c_int64, [C.POINTER(Dims)]),
     "ppo_update_minibatch": (C.c_int, [_P, C.POINTER(Dims), _P, _P, _P, _P, _P, _P, _P, _P, C.c_int64, C.c_int,

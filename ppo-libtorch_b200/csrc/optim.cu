@@ -120,6 +120,62 @@ __global__ void __launch_bounds__(STAT_THREADS) adv_stats_kernel(const float* __
     }
 }
 
+// Sliced variant: ADV_SLICES CTAs per minibatch accumulate raw moments in double; the last CTA of a minibatch to
+// finish (ticket) sums the slices in fixed order and writes the statistics.  workspace = [n_mb][ADV_SLICES][2] doubles
+// + [n_mb] uint32 tickets, zeroed once by the caller and left zeroed.
+constexpr int ADV_SLICES = 32, ADV_THREADS = 256;
+__global__ void __launch_bounds__(ADV_THREADS) adv_moments_kernel(const float* __restrict__ adv,
+                                                                  const int32_t* __restrict__ perm, int64_t batch,
+                                                                  int mb_size, int n_mb, double* __restrict__ ws,
+                                                                  float* __restrict__ stats_out,
+                                                                  double* __restrict__ partial_out) {
+    __shared__ double sh[ADV_THREADS / 32];
+    __shared__ bool last;
+    const int mb = blockIdx.x, sl = blockIdx.y;
+    const int64_t start = (int64_t)mb * mb_size;
+    int64_t cnt = batch - start;
+    if (cnt > mb_size) cnt = mb_size;
+    if (cnt < 0) cnt = 0;
+    const int64_t per = (cnt + ADV_SLICES - 1) / ADV_SLICES;
+    const int64_t i0 = sl * per, i1 = i0 + per < cnt ? i0 + per : cnt;
+    double s = 0.0, q = 0.0;
+    for (int64_t i = i0 + threadIdx.x; i < i1; i += ADV_THREADS) {
+        const int64_t r = perm ? (int64_t)perm[start + i] : start + i;
+        const double x = (double)__ldg(adv + r);
+        s += x;
+        q += x * x;
+    }
+    s = block_sum<ADV_THREADS>(s, sh);
+    q = block_sum<ADV_THREADS>(q, sh);
+    unsigned int* tickets = reinterpret_cast<unsigned int*>(ws + (size_t)n_mb * ADV_SLICES * 2);
+    if (threadIdx.x == 0) {
+        ws[((size_t)mb * ADV_SLICES + sl) * 2 + 0] = s;
+        ws[((size_t)mb * ADV_SLICES + sl) * 2 + 1] = q;
+        __threadfence();
+        last = (atomicAdd(tickets + mb, 1u) == ADV_SLICES - 1);
+    }
+    __syncthreads();
+    if (!last || threadIdx.x != 0) return;
+    __threadfence();
+    double S = 0.0, Q = 0.0;
+    for (int k = 0; k < ADV_SLICES; k++) {
+        S += ws[((size_t)mb * ADV_SLICES + k) * 2 + 0];
+        Q += ws[((size_t)mb * ADV_SLICES + k) * 2 + 1];
+    }
+    tickets[mb] = 0;
+    const double n = (double)cnt;
+    if (partial_out) {
+        partial_out[mb * 3 + 0] = n; partial_out[mb * 3 + 1] = S; partial_out[mb * 3 + 2] = Q;
+    }
+    if (stats_out) {
+        const double mean = cnt > 0 ? S / n : 0.0;
+        double var = (Q - n * mean * mean) / (n - 1.0);
+        if (var < 0.0) var = 0.0;
+        stats_out[mb * 2 + 0] = (float)mean;
+        stats_out[mb * 2 + 1] = (float)sqrt(var);
+    }
+}
+
 __global__ void adv_stats_finalize_kernel(const double* __restrict__ partial, int n_mb, float* __restrict__ stats_out) {
     const int mb = blockIdx.x * blockDim.x + threadIdx.x;
     if (mb >= n_mb) return;
@@ -234,12 +290,20 @@ extern "C" int ppo_clip_adamw(float* params, float* grads, float* exp_avg, float
                              step, d_step, max_grad_norm, grad_scale, norm_out, nullptr, nullptr, as_stream(stream));
 }
 
+extern "C" int64_t ppo_adv_stats_workspace_bytes(int n_mb) {
+    return n_mb < 0 ? -1 : (int64_t)n_mb * ADV_SLICES * 2 * (int64_t)sizeof(double) + (int64_t)n_mb * 4 + 16;
+}
+
 extern "C" int ppo_adv_stats(const float* adv, const int32_t* perm, int64_t batch, int mb_size, int n_mb,
-                             float* stats_out, double* partial_out, ppo_stream_t stream) {
+                             float* stats_out, double* partial_out, void* workspace, ppo_stream_t stream) {
     PPO_REQUIRE(adv && mb_size >= 1 && n_mb >= 0 && batch >= 0, "ppo_adv_stats: bad arguments");
     PPO_REQUIRE(stats_out || partial_out, "ppo_adv_stats: no output requested");
     if (n_mb == 0) return PPO_OK;
-    adv_stats_kernel<<<n_mb, STAT_THREADS, 0, as_stream(stream)>>>(adv, perm, batch, mb_size, stats_out, partial_out);
+    if (workspace && mb_size >= 4 * ADV_SLICES * ADV_THREADS)
+        adv_moments_kernel<<<dim3(n_mb, ADV_SLICES), ADV_THREADS, 0, as_stream(stream)>>>(
+            adv, perm, batch, mb_size, n_mb, reinterpret_cast<double*>(workspace), stats_out, partial_out);
+    else
+        adv_stats_kernel<<<n_mb, STAT_THREADS, 0, as_stream(stream)>>>(adv, perm, batch, mb_size, stats_out, partial_out);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
 }

@@ -61,7 +61,7 @@ struct ppo_trainer {
     uint8_t* masks;
     float *adv_stats, *diag_hist, *ev_out, *norm_out;
     double *adv_partial, *ep_stats;
-    void *upd_ws, *ev_ws;
+    void *upd_ws, *ev_ws, *adv_ws;
     Scalars* d_scal;
     // host
     float* h_diag = nullptr;    // pinned [n_opt, 8]
@@ -179,6 +179,7 @@ extern "C" ppo_trainer* ppo_trainer_create(const ppo_trainer_cfg* c) {
         {"scalars", (void**)&t->d_scal, sizeof(Scalars)},
         {"upd_ws", (void**)&t->upd_ws, (size_t)ppo_update_workspace_bytes(&c->dims)},
         {"ev_ws", (void**)&t->ev_ws, (size_t)ppo_explained_variance_workspace_bytes()},
+        {"adv_ws", (void**)&t->adv_ws, (size_t)ppo_adv_stats_workspace_bytes(t->n_mb)},
     };
     size_t total = 0;
     for (auto& it : items) total += al256(it.bytes);
@@ -306,13 +307,13 @@ static int phase_begin_epoch(ppo_trainer* t, int epoch, cudaStream_t st) {
     if (rc) return rc;
     if (!c.hyper.norm_adv) return PPO_OK;
     if (c.world_size > 1 && t->comm) {
-        rc = ppo_adv_stats(t->adv, t->perm, t->B, t->mb_size, t->n_mb, nullptr, t->adv_partial, st);
+        rc = ppo_adv_stats(t->adv, t->perm, t->B, t->mb_size, t->n_mb, nullptr, t->adv_partial, t->adv_ws, st);
         if (rc) return rc;
         rc = ppo_comm_allreduce_f64(t->comm, t->adv_partial, (int64_t)t->n_mb * 3, st);
         if (rc) return rc;
         return ppo_adv_stats_finalize(t->adv_partial, t->n_mb, t->adv_stats, st);
     }
-    return ppo_adv_stats(t->adv, t->perm, t->B, t->mb_size, t->n_mb, t->adv_stats, nullptr, st);
+    return ppo_adv_stats(t->adv, t->perm, t->B, t->mb_size, t->n_mb, t->adv_stats, nullptr, t->adv_ws, st);
 }
 
 static int phase_minibatch_grads(ppo_trainer* t, int mb, cudaStream_t st) {

@@ -110,19 +110,38 @@ __global__ void __launch_bounds__(MLP_THREADS) update_kernel(const UpdArgs a) {
     }
 }
 
-// grads_out[i] = sum over CTAs (fixed order, double accumulation) of slab[cta][i]; the last block also
-// turns the diagnostic partials into diag_out = {pg_loss, v_loss, entropy, loss, approx_kl, clipfrac, 0, 0}.
-__global__ void __launch_bounds__(256) reduce_kernel(const float* __restrict__ slabs, const double* __restrict__ dpart,
-                                                     int nslabs, int P, int64_t stride, float inv_n, float ent_coef,
-                                                     float vf_coef, float* __restrict__ grads_out,
-                                                     float* __restrict__ diag_out) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+// grads_out[i] = sum over CTAs (fixed order, double accumulation) of slab[cta][i]; block 0 also turns the diagnostic
+// partials into diag_out = {pg_loss, v_loss, entropy, loss, approx_kl, clipfrac, 0, 0}.
+// A block owns RED_COLS consecutive parameters; its 256 threads split the slabs RED_PARTS ways (coalesced 256-byte
+// rows, independent loads in flight), then combine the RED_PARTS partial sums in fixed order.
+constexpr int RED_COLS = 64, RED_PARTS = 4;
+__global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_kernel(
+    const float* __restrict__ slabs, const double* __restrict__ dpart, int nslabs, int P, int64_t stride, float inv_n,
+    float ent_coef, float vf_coef, float* __restrict__ grads_out, float* __restrict__ diag_out) {
+    __shared__ double part[RED_PARTS][RED_COLS];
+    const int col = threadIdx.x & (RED_COLS - 1), pt = threadIdx.x / RED_COLS;
+    const int i = blockIdx.x * RED_COLS + col;
+    double acc = 0.0;
     if (i < P) {
-        double acc = 0.0;
-        for (int s = 0; s < nslabs; s++) acc += (double)slabs[(size_t)s * stride + i];
-        grads_out[i] = (float)acc;
+        const int per = (nslabs + RED_PARTS - 1) / RED_PARTS;
+        const int s0 = pt * per, s1 = min(nslabs, s0 + per);
+        const float* p = slabs + (size_t)s0 * stride + i;
+        int s = s0;
+        for (; s + 4 <= s1; s += 4, p += 4 * stride) {
+            const float a0 = p[0], a1 = p[stride], a2 = p[2 * stride], a3 = p[3 * stride];
+            acc += (double)a0; acc += (double)a1; acc += (double)a2; acc += (double)a3;
+        }
+        for (; s < s1; s++, p += stride) acc += (double)p[0];
     }
-    if (blockIdx.x == gridDim.x - 1 && threadIdx.x < 32 && diag_out) {
+    part[pt][col] = acc;
+    __syncthreads();
+    if (pt == 0 && i < P) {
+        double t = part[0][col];
+#pragma unroll
+        for (int q = 1; q < RED_PARTS; q++) t += part[q][col];
+        grads_out[i] = (float)t;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < 32 && diag_out) {
         double v = 0.0;
         if (threadIdx.x < 5)
             for (int s = 0; s < nslabs; s++) v += dpart[(size_t)s * UPD_NDIAG + threadIdx.x];
@@ -138,6 +157,10 @@ __global__ void __launch_bounds__(256) reduce_kernel(const float* __restrict__ s
             diag_out[4] = kl; diag_out[5] = cf; diag_out[6] = 0.0f; diag_out[7] = 0.0f;
         }
     }
+}
+static inline void launch_reduce(const UpdArgs& a, int grid, int P, float* grads_out, float* diag_out, cudaStream_t st) {
+    reduce_kernel<<<(P + RED_COLS - 1) / RED_COLS, RED_COLS * RED_PARTS, 0, st>>>(
+        a.slabs, a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out);
 }
 
 template <int TM, int H>
@@ -157,8 +180,7 @@ static int launch_update(const UpdArgs& a, float* grads_out, float* diag_out, cu
     update_kernel<TM, H><<<grid, MLP_THREADS, smem, st>>>(a);
     PPO_LAUNCH_CHECK();
     const int P = num_params(a.d.O, a.d.H, a.d.K);
-    reduce_kernel<<<(P + 255) / 256, 256, 0, st>>>(a.slabs, a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef,
-                                                   a.hp.vf_coef, grads_out, diag_out);
+    launch_reduce(a, grid, P, grads_out, diag_out, st);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
 }
@@ -200,8 +222,7 @@ extern "C" int ppo_update_minibatch(const float* params, const ppo_dims* dims, c
         int grid = 0;
         const int rc = launch_update_tc(a, mode == PPO_MATH_BF16 ? 1 : 0, &grid, st);
         if (rc == PPO_OK) {
-            reduce_kernel<<<(P + 255) / 256, 256, 0, st>>>(a.slabs, a.dpart, grid, P, slab_stride(P), a.inv_n,
-                                                           a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out);
+            launch_reduce(a, grid, P, grads_out, diag_out, st);
             PPO_LAUNCH_CHECK();
             return PPO_OK;
         }

@@ -154,11 +154,22 @@ def rollout(params, obs_dim, hidden, nvec, env_kind, state, ep_len, ep_ret, next
 
 
 # ---- update (K5, K6) -------------------------------------------------------------------------------
-def adv_stats(adv, mb_size, n_mb, perm=None):
+_adv_ws = {}
+
+
+def _adv_workspace(n_mb, dev):
+    key = (n_mb, dev.index)
+    if key not in _adv_ws:
+        _adv_ws[key] = torch.zeros(load().ppo_adv_stats_workspace_bytes(n_mb), dtype=torch.uint8, device=dev)
+    return _adv_ws[key]
+
+
+def adv_stats(adv, mb_size, n_mb, perm=None, workspace=True):
     """per-minibatch advantage mean / unbiased std -> float32 [n_mb, 2]"""
     _cuda_required()
     out = torch.empty((n_mb, 2), dtype=torch.float32, device=adv.device)
-    check(load().ppo_adv_stats(ptr(adv), ptr(perm), adv.numel(), mb_size, n_mb, ptr(out), None, stream_ptr()))
+    ws = _adv_workspace(n_mb, adv.device) if workspace else None
+    check(load().ppo_adv_stats(ptr(adv), ptr(perm), adv.numel(), mb_size, n_mb, ptr(out), None, ptr(ws), stream_ptr()))
     return out
 
 
@@ -166,7 +177,8 @@ def adv_partials(adv, mb_size, n_mb, perm=None):
     """raw per-minibatch moments {count, sum, sum of squares} (float64 [n_mb,3]) for the data-parallel merge"""
     _cuda_required()
     out = torch.empty((n_mb, 3), dtype=torch.float64, device=adv.device)
-    check(load().ppo_adv_stats(ptr(adv), ptr(perm), adv.numel(), mb_size, n_mb, None, ptr(out), stream_ptr()))
+    check(load().ppo_adv_stats(ptr(adv), ptr(perm), adv.numel(), mb_size, n_mb, None, ptr(out),
+                               ptr(_adv_workspace(n_mb, adv.device)), stream_ptr()))
     return out
 
 

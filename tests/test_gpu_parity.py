@@ -397,6 +397,25 @@ def test_adv_partials_merge(P):
         close(st[mb], [x.mean().item(), x.std(unbiased=True).item()], rtol=1e-6)
 
 
+@pytest.mark.parametrize("mb_size,n_mb,ragged", [(131072, 4, 0), (40000, 3, 777)])
+def test_adv_stats_sliced_equals_two_pass(P, mb_size, n_mb, ragged):
+    """large minibatches: 32 CTAs per minibatch on raw double moments (workspace) against the one-CTA two-pass kernel
+    and against numpy, through a permutation, with a short last minibatch"""
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    batch = mb_size * n_mb - ragged
+    a = torch.randn(batch, device="cuda", generator=gen) * 3 + 1
+    perm = torch.randperm(batch, device="cuda", generator=gen).to(torch.int32)
+    fast = P.ops.adv_stats(a, mb_size, n_mb, perm=perm, workspace=True).cpu().numpy()
+    slow = P.ops.adv_stats(a, mb_size, n_mb, perm=perm, workspace=False).cpu().numpy()
+    close(fast, slow, rtol=1e-6)
+    x = a[perm.long()].double().cpu().numpy()
+    for mb in range(n_mb):
+        seg = x[mb * mb_size:(mb + 1) * mb_size]
+        close(fast[mb], [seg.mean(), seg.std(ddof=1)], rtol=1e-6)
+    again = P.ops.adv_stats(a, mb_size, n_mb, perm=perm, workspace=True).cpu().numpy()
+    assert np.array_equal(fast, again)          # tickets were reset; fixed-order sums
+
+
 def test_explained_variance(P, orc):
     rng = np.random.default_rng(0)
     for n in (2, 1000, 524288):
