@@ -306,6 +306,10 @@ int ppo_trainer_set_comm(ppo_trainer* t, ppo_comm* comm);
  * D receives the raw tensor-memory image [128 lanes][64 columns] (M = 64 results sit in lanes
  * (m % 16) + 32 (m / 16)).  No reference counterpart. */
 int ppo_debug_umma_probe(int mode, int fmt, const float* A, const float* B, float* D, ppo_stream_t stream);
+/* Same GEMM issued `reps` times back to back by one thread; d_cycles[0] (device int64) = SM clocks from the first issue
+ * to the completion of the last (how fast the tensor pipe retires each operand layout). */
+int ppo_debug_umma_time(int mode, int fmt, const float* A, const float* B, float* D, int reps, long long* d_cycles,
+                        ppo_stream_t stream);
 
 #ifdef __cplusplus
 }

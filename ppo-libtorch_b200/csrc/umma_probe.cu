@@ -5,6 +5,7 @@
 //   mode 1: D[128,64] = A[128,64] * B[64,64]     A K-major, B MN-major       (backward dX = dY W)
 //   mode 2: D[64,64]  = A[128,64]^T * B[128,64]  A MN-major (M = 64), B MN-major (backward dW = dY^T X)
 //   mode 3: D[64,16]  = A[128,64]^T * B[128,16]  B = narrow tile of 2 chunks, N = 16   (dW1 / db / dW3)
+//   mode 4: mode 2 with the accumulator placed at lane offset 16 (two M = 64 accumulators interleaved in lanes)
 // D comes back as the raw tensor-memory image out[lane][col] (128 x 64); tests/test_gpu_tensorcore.py maps
 // M = 64 rows to lanes (m % 16) + 32 * (m / 16).
 #include "common.cuh"
@@ -23,7 +24,8 @@ __device__ inline void store_row_chunk(uint8_t* dst, const float* src) {  // 8 f
 
 template <int FMT>
 __global__ void __launch_bounds__(128) umma_probe_kernel(int mode, const float* __restrict__ A,
-                                                         const float* __restrict__ B, float* __restrict__ out) {
+                                                         const float* __restrict__ B, float* __restrict__ out, int reps,
+                                                         long long* __restrict__ cycles) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // swizzle atoms need 1024 B alignment
     uint8_t* sA = smem;                 // activation tile, 128 rows x 128 B = 16 KB
@@ -42,7 +44,7 @@ __global__ void __launch_bounds__(128) umma_probe_kernel(int mode, const float* 
     if (mode == 0 || mode == 1) {
         if (t < 64)
             for (int c = 0; c < 8; c++) store_row_chunk<FMT>(sB + act_chunk_off(t, c), B + t * 64 + c * 8);
-    } else if (mode == 2) {
+    } else if (mode == 2 || mode == 4) {
         for (int c = 0; c < 8; c++) store_row_chunk<FMT>(sB + act_chunk_off(t, c), B + t * 64 + c * 8);
     } else {
         for (int c = 0; c < 2; c++) store_row_chunk<FMT>(sB + c * (128 * 16) + t * 16, B + t * 16 + c * 8);
@@ -53,25 +55,31 @@ __global__ void __launch_bounds__(128) umma_probe_kernel(int mode, const float* 
     tc_fence_after();
     const uint32_t tm = tmem_base_s;
 
+    long long t0 = 0;
     if (t == 0) {
         const uint32_t a = smem_u32(sA), b = smem_u32(sB);
-        if (mode == 0) {
-            const uint32_t id = idesc_f16(FMT, 128, 64, 0, 0);
-            for (int ks = 0; ks < 4; ks++) mma_f16(tm, act_desc_kmajor(a, ks), act_desc_kmajor(b, ks), id, ks > 0);
-        } else if (mode == 1) {
-            const uint32_t id = idesc_f16(FMT, 128, 64, 0, 1);
-            for (int ks = 0; ks < 4; ks++) mma_f16(tm, act_desc_kmajor(a, ks), act_desc_mnmajor(b, ks), id, ks > 0);
-        } else if (mode == 2) {
-            const uint32_t id = idesc_f16(FMT, 64, 64, 1, 1);
-            for (int ks = 0; ks < 8; ks++) mma_f16(tm, act_desc_mnmajor(a, ks), act_desc_mnmajor(b, ks), id, ks > 0);
-        } else {
-            const uint32_t id = idesc_f16(FMT, 64, 16, 1, 1);
-            for (int ks = 0; ks < 8; ks++)
-                mma_f16(tm, act_desc_mnmajor(a, ks), narrow_desc_mnmajor(b, 128, ks), id, ks > 0);
+        t0 = clock64();
+        for (int rep = 0; rep < reps; rep++) {  // reps > 1: timing only (the accumulator keeps the last repetition)
+            if (mode == 0) {
+                const uint32_t id = idesc_f16(FMT, 128, 64, 0, 0);
+                for (int ks = 0; ks < 4; ks++) mma_f16(tm, act_desc_kmajor(a, ks), act_desc_kmajor(b, ks), id, ks > 0);
+            } else if (mode == 1) {
+                const uint32_t id = idesc_f16(FMT, 128, 64, 0, 1);
+                for (int ks = 0; ks < 4; ks++) mma_f16(tm, act_desc_kmajor(a, ks), act_desc_mnmajor(b, ks), id, ks > 0);
+            } else if (mode == 2 || mode == 4) {  // mode 4: the accumulator in the upper half-subpartitions (lanes +16)
+                const uint32_t id = idesc_f16(FMT, 64, 64, 1, 1);
+                const uint32_t dst = mode == 4 ? tm + (16u << 16) : tm;
+                for (int ks = 0; ks < 8; ks++) mma_f16(dst, act_desc_mnmajor(a, ks), act_desc_mnmajor(b, ks), id, ks > 0);
+            } else {
+                const uint32_t id = idesc_f16(FMT, 64, 16, 1, 1);
+                for (int ks = 0; ks < 8; ks++)
+                    mma_f16(tm, act_desc_mnmajor(a, ks), narrow_desc_mnmajor(b, 128, ks), id, ks > 0);
+            }
         }
         mma_commit(&bar);
     }
     mbar_wait(&bar, 0);
+    if (t == 0 && cycles) cycles[0] = clock64() - t0;
     tc_fence_after();
     float v[64];
 #pragma unroll
@@ -86,17 +94,27 @@ __global__ void __launch_bounds__(128) umma_probe_kernel(int mode, const float* 
 
 }  // namespace ppo
 
+static int probe_launch(int mode, int fmt, const float* A, const float* B, float* D, int reps, long long* cycles,
+                        ppo_stream_t stream);
 extern "C" int ppo_debug_umma_probe(int mode, int fmt, const float* A, const float* B, float* D, ppo_stream_t stream) {
+    return probe_launch(mode, fmt, A, B, D, 1, nullptr, stream);
+}
+extern "C" int ppo_debug_umma_time(int mode, int fmt, const float* A, const float* B, float* D, int reps,
+                                   long long* d_cycles, ppo_stream_t stream) {
+    return probe_launch(mode, fmt, A, B, D, reps, d_cycles, stream);
+}
+static int probe_launch(int mode, int fmt, const float* A, const float* B, float* D, int reps, long long* cycles,
+                        ppo_stream_t stream) {
     using namespace ppo;
-    PPO_REQUIRE(mode >= 0 && mode <= 3 && (fmt == 0 || fmt == 1) && A && B && D, "ppo_debug_umma_probe: bad argument");
+    PPO_REQUIRE(mode >= 0 && mode <= 4 && (fmt == 0 || fmt == 1) && A && B && D, "ppo_debug_umma_probe: bad argument");
     static bool attr_done = false;
     if (!attr_done) {
         PPO_CUDA(cudaFuncSetAttribute(umma_probe_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 40960));
         PPO_CUDA(cudaFuncSetAttribute(umma_probe_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 40960));
         attr_done = true;
     }
-    if (fmt == 0) umma_probe_kernel<0><<<1, 128, 40960, as_stream(stream)>>>(mode, A, B, D);
-    else umma_probe_kernel<1><<<1, 128, 40960, as_stream(stream)>>>(mode, A, B, D);
+    if (fmt == 0) umma_probe_kernel<0><<<1, 128, 40960, as_stream(stream)>>>(mode, A, B, D, reps, cycles);
+    else umma_probe_kernel<1><<<1, 128, 40960, as_stream(stream)>>>(mode, A, B, D, reps, cycles);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
 }

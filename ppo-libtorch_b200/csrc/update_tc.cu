@@ -6,9 +6,11 @@
 // fp32 accumulation in tensor memory); everything per-sample (layer 1, bias + tanh, the output layer, softmax /
 // ratio / clipping / value loss, the tanh derivatives) runs one-thread-per-row on the CUDA cores.
 //
-// CTA = NWG compute warpgroups (128 threads = 128 minibatch rows each) + 1 MMA-issuer warp.  A warpgroup walks its
-// 128-row tiles; per tile and net it hands four operand stages to the issuer through an mbarrier ("ready") and gets
-// completions back through two more ("doneZ": an accumulator it must read; "doneW": operands it may overwrite):
+// CTA = NWG warpgroups (128 threads = 128 minibatch rows each).  A warpgroup walks its 128-row tiles; per tile and
+// net it writes four operand stages to shared memory, and after a warpgroup-wide named barrier its thread 0 issues
+// the stage's MMAs (measured: one issuer warp serving all warpgroups was itself the bottleneck, ~1100 dependent
+// instructions per tile).  Completions come back through two mbarriers per warpgroup ("doneZ": an accumulator it must
+// read; "doneW": operands it may overwrite):
 //   S1  h1 = tanh([x,1] P1^T)            -> A1          G1 : Z   = A1 W2^T                        (doneZ)
 //   S2  h2 = tanh(Z + b2) -> A2, logits/value, loss, dOut -> DO
 //                                                        G5 : dW3^T += A2^T DO                     (doneW)
@@ -16,8 +18,8 @@
 //                                                        G3 : dW2 += A3^T A1 ; d[.|b2] += A3^T XE   (doneW)
 //   S4  dZ1 = Z (1 - h1^2)               -> A2          G4 : d[W1|b1] += A2^T XE                  (doneW)
 // While one warpgroup waits on the tensor core another computes, so the two pipes overlap without a software
-// pipeline inside a warpgroup.  All weight-gradient accumulators stay in tensor memory for the whole kernel (one
-// issuing thread => in-order accumulation) and are drained once into the CTA's slab; reduce_kernel (update.cu) sums
+// pipeline inside a warpgroup.  All weight-gradient accumulators stay in tensor memory for the whole kernel (private
+// to a warpgroup, one issuing thread each => in-order accumulation) and are drained once into the CTA's slab; reduce_kernel (update.cu) sums
 // the slabs in fixed order, so results are run-to-run identical.  Gradients are kept un-normalised (no 1/n) until
 // the drain so that fp16 operands do not underflow.
 #include "ppo_loss.cuh"
@@ -99,84 +101,55 @@ __device__ __forceinline__ TcCols tc_cols(int nwg, int g, int net, int n3a) {
     return TcCols{base, base + 64u, base + 72u, base + 80u};
 }
 
-// ---- the MMA issuer (one thread): serves every warpgroup's stages in arrival order ------------------------------
-template <int FMT, int NWG>
-__device__ inline void tc_issuer(uint8_t* sm, const TcLayout& L, uint64_t* bars, uint32_t tmem, int K, int ntiles) {
-    const uint32_t sbase = smem_u32(sm);
-    const int nwg_total = gridDim.x * NWG;
-    int remaining[NWG], stage[NWG];
-    uint32_t phase[NWG];
-    int total = 0;
+// ---- MMA issue: thread 0 of a warpgroup issues that warpgroup's stage (its accumulators are private, so no ordering
+// between the issuing threads of different warpgroups is needed).  Descriptors are precomputed; a K-step only adds a
+// constant to the start-address field (16-byte units).
+struct WgDescs {
+    uint64_t a1k, a1m, a2m, a3k, a3m, xe, dout;  // activation tiles (K-major / MN-major views), narrow tiles
+    uint64_t w2k[2], w2m[2];                      // W2 of actor / critic
+    uint32_t Z;                                   // tensor-memory address of this warpgroup's Z block
+    TcCols c[2];
+    uint32_t id_w3[2];
+    uint32_t fresh;                               // bit (net * 4 + accumulator): next MMA into it must overwrite
+};
+template <int FMT, int ST>
+__device__ __forceinline__ void issue_stage(WgDescs& d, int net, uint32_t tmem, uint64_t* doneZ, uint64_t* doneW) {
+    constexpr uint32_t id_fwd = idesc_f16(FMT, 128, 64, 0, 0);   // Z = A1 W2^T
+    constexpr uint32_t id_dx = idesc_f16(FMT, 128, 64, 0, 1);    // Z = A3 W2
+    constexpr uint32_t id_dw = idesc_f16(FMT, 64, 64, 1, 1);     // dW2 += A3^T A1
+    constexpr uint32_t id_n8 = idesc_f16(FMT, 64, 8, 1, 1);      // skinny, N = 8
+    const uint32_t fb = (uint32_t)net * 4u;
+    const TcCols c = d.c[net];
+    tc_fence_after();
+    if (ST == 0) {
 #pragma unroll
-    for (int g = 0; g < NWG; g++) {
-        const int wgid = blockIdx.x * NWG + g;
-        const int tiles = wgid < ntiles ? (ntiles - wgid + nwg_total - 1) / nwg_total : 0;
-        remaining[g] = tiles * 8;  // 2 nets x 4 stages
-        stage[g] = 0;
-        phase[g] = 0;
-        total += remaining[g];
-    }
-    uint32_t fresh[NWG];     // bit (net * 4 + accumulator): the next MMA into it must overwrite
+        for (int ks = 0; ks < 4; ks++) mma_f16(d.Z, d.a1k + 2u * ks, d.w2k[net] + 2u * ks, id_fwd, ks > 0);
+        mma_commit(doneZ);
+    } else if (ST == 1) {
+        const uint32_t acc0 = (d.fresh >> (fb + 3)) & 1u ? 0u : 1u;
 #pragma unroll
-    for (int g = 0; g < NWG; g++) fresh[g] = 0xFFu;
-    const uint32_t id_fwd = idesc_f16(FMT, 128, 64, 0, 0);   // Z = A1 W2^T
-    const uint32_t id_dx = idesc_f16(FMT, 128, 64, 0, 1);    // Z = A3 W2
-    const uint32_t id_dw = idesc_f16(FMT, 64, 64, 1, 1);     // dW2 += A3^T A1
-    const uint32_t id_n8 = idesc_f16(FMT, 64, 8, 1, 1);      // skinny, N = 8
-    const uint32_t id_w3a = idesc_f16(FMT, 64, (K + 7) & ~7, 1, 1);
-    while (total > 0) {
+        for (int ks = 0; ks < 8; ks++)
+            mma_f16(tmem + c.w3, d.a2m + 128u * ks, d.dout + 16u * ks, d.id_w3[net], ks > 0 ? 1u : acc0);
+        d.fresh &= ~(1u << (fb + 3));
+        mma_commit(doneW);
+    } else if (ST == 2) {
 #pragma unroll
-        for (int g = 0; g < NWG; g++) {
-            if (remaining[g] == 0) continue;
-            uint64_t* ready = bars + g;
-            if (!mbar_test(ready, phase[g] & 1u)) continue;
-            tc_fence_after();
-            const int st = stage[g] & 3, net = (stage[g] >> 2) & 1;
-            const uint32_t wg = sbase + (uint32_t)(L.wg0 + g * L.wg_stride);
-            const uint32_t A1 = wg + L.a1, A2 = wg + L.a2, A3 = wg + L.a3, XE = wg + L.xe, DO = wg + L.dout;
-            const uint32_t W2 = sbase + (uint32_t)L.w2[net];
-            const uint32_t Z = tmem + (uint32_t)g * 64u;
-            const TcCols c = tc_cols(NWG, g, net, L.n3a);
-            const uint32_t fb = (uint32_t)net * 4u;
-            if (st == 0) {
+        for (int ks = 0; ks < 4; ks++) mma_f16(d.Z, d.a3k + 2u * ks, d.w2m[net] + 128u * ks, id_dx, ks > 0);
+        mma_commit(doneZ);
+        const uint32_t acc0 = (d.fresh >> fb) & 1u ? 0u : 1u;
 #pragma unroll
-                for (int ks = 0; ks < 4; ks++) mma_f16(Z, act_desc_kmajor(A1, ks), act_desc_kmajor(W2, ks), id_fwd, ks > 0);
-                mma_commit(bars + NWG + g);
-            } else if (st == 1) {
-                const uint32_t acc0 = (fresh[g] >> (fb + 3)) & 1u ? 0u : 1u;
-#pragma unroll
-                for (int ks = 0; ks < 8; ks++)
-                    mma_f16(tmem + c.w3, act_desc_mnmajor(A2, ks), narrow_desc_mnmajor(DO, TC_ROWS, ks),
-                            net == 0 ? id_w3a : id_n8, ks > 0 ? 1u : acc0);
-                fresh[g] &= ~(1u << (fb + 3));
-                mma_commit(bars + 2 * NWG + g);
-            } else if (st == 2) {
-#pragma unroll
-                for (int ks = 0; ks < 4; ks++) mma_f16(Z, act_desc_kmajor(A3, ks), act_desc_mnmajor(W2, ks), id_dx, ks > 0);
-                mma_commit(bars + NWG + g);
-                const uint32_t acc0 = (fresh[g] >> fb) & 1u ? 0u : 1u;
-#pragma unroll
-                for (int ks = 0; ks < 8; ks++) {
-                    mma_f16(tmem + c.w2, act_desc_mnmajor(A3, ks), act_desc_mnmajor(A1, ks), id_dw, ks > 0 ? 1u : acc0);
-                    mma_f16(tmem + c.xe2, act_desc_mnmajor(A3, ks), narrow_desc_mnmajor(XE, TC_ROWS, ks), id_n8,
-                            ks > 0 ? 1u : acc0);
-                }
-                fresh[g] &= ~(3u << fb);
-                mma_commit(bars + 2 * NWG + g);
-            } else {
-                const uint32_t acc0 = (fresh[g] >> (fb + 2)) & 1u ? 0u : 1u;
-#pragma unroll
-                for (int ks = 0; ks < 8; ks++)
-                    mma_f16(tmem + c.xe1, act_desc_mnmajor(A2, ks), narrow_desc_mnmajor(XE, TC_ROWS, ks), id_n8,
-                            ks > 0 ? 1u : acc0);
-                fresh[g] &= ~(1u << (fb + 2));
-                mma_commit(bars + 2 * NWG + g);
-            }
-            stage[g]++;
-            phase[g]++;
-            remaining[g]--;
-            total--;
+        for (int ks = 0; ks < 8; ks++) {
+            mma_f16(tmem + c.w2, d.a3m + 128u * ks, d.a1m + 128u * ks, id_dw, ks > 0 ? 1u : acc0);
+            mma_f16(tmem + c.xe2, d.a3m + 128u * ks, d.xe + 16u * ks, id_n8, ks > 0 ? 1u : acc0);
         }
+        d.fresh &= ~(3u << fb);
+        mma_commit(doneW);
+    } else {
+        const uint32_t acc0 = (d.fresh >> (fb + 2)) & 1u ? 0u : 1u;
+#pragma unroll
+        for (int ks = 0; ks < 8; ks++) mma_f16(tmem + c.xe1, d.a2m + 128u * ks, d.xe + 16u * ks, id_n8, ks > 0 ? 1u : acc0);
+        d.fresh &= ~(1u << (fb + 2));
+        mma_commit(doneW);
     }
 }
 
@@ -198,50 +171,81 @@ __device__ __forceinline__ void layer1_chunk(const float* P1, const float (&xe)[
 }
 
 template <int FMT, int NWG>
-__global__ void __launch_bounds__(NWG * 128 + 32, 1) update_tc_kernel(const UpdArgs a) {
+__global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const int O = a.d.O, K = a.d.K, heads = a.d.heads;
     const TcLayout L = tc_layout(K, NWG);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const bool issuer_warp = warp == NWG * 4;
     const NetOff offs[2] = {actor_off(O, TC_H, K), critic_off(O, TC_H)};
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + L.bars);  // ready[g], doneZ[NWG + g], doneW[2 NWG + g]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + L.bars);  // doneZ[NWG + g], doneW[2 NWG + g]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + L.tmem_slot);
     const int ntiles = (a.mb_size + TC_ROWS - 1) / TC_ROWS;
-    const int nthreads = NWG * 128 + 32;
+    const int nthreads = NWG * 128;
 
     // ---------------- prologue: tensor memory, barriers, parameters -> shared memory -------------------------
-    if (issuer_warp) tmem_alloc(tmem_slot, 512);
+    if (warp == 0) tmem_alloc(tmem_slot, 512);
     if (tid == 0) {
         for (int g = 0; g < NWG; g++) {
-            mbar_init(bars + g, 128);
             mbar_init(bars + NWG + g, 1);
             mbar_init(bars + 2 * NWG + g, 1);
         }
         mbar_init_fence();
     }
-    for (int e = tid; e < 2 * 64 * 8; e += nthreads) {  // W2 of both nets as 16-bit activation-layout tiles
-        const int net = e >> 9, row = (e >> 3) & 63, chunk = e & 7;
-        const float* src = a.params + offs[net].W2 + row * TC_H + chunk * 8;
-        float v[8];
+    {   // W2 of both nets as 16-bit activation-layout tiles: 1024 chunk tasks, all loads of a thread in flight together
+        constexpr int W2_IT = (2 * 64 * 8 + NWG * 128 - 1) / (NWG * 128);
+        float v[W2_IT][8];
 #pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = __ldg(src + i);
-        store8<FMT>(sm + L.w2[net] + act_chunk_off(row, chunk), v);
-    }
-    for (int net = 0; net < 2; net++) {
-        const int k3 = net == 0 ? K : 1;
-        float* P1 = reinterpret_cast<float*>(sm + L.p1[net]);
-        for (int e = tid; e < TC_H * 8; e += nthreads) {
-            const int j = e >> 3, i = e & 7;
-            P1[e] = i < O ? __ldg(a.params + offs[net].W1 + j * O + i) : (i == O ? __ldg(a.params + offs[net].b1 + j) : 0.0f);
+        for (int it = 0; it < W2_IT; it++) {
+            const int e = tid + it * nthreads;
+            if (e < 2 * 64 * 8) {
+                const float* src = a.params + offs[e >> 9].W2 + ((e >> 3) & 63) * TC_H + (e & 7) * 8;
+#pragma unroll
+                for (int i = 0; i < 8; i++) v[it][i] = __ldg(src + i);
+            }
         }
-        float* B2 = reinterpret_cast<float*>(sm + L.b2[net]);
-        for (int e = tid; e < TC_H; e += nthreads) B2[e] = __ldg(a.params + offs[net].b2 + e);
-        float* W3 = reinterpret_cast<float*>(sm + L.w3[net]);
-        for (int e = tid; e < k3 * TC_H; e += nthreads) W3[e] = __ldg(a.params + offs[net].W3 + e);
-        float* B3 = reinterpret_cast<float*>(sm + L.b3p[net]);
-        for (int e = tid; e < k3; e += nthreads) B3[e] = __ldg(a.params + offs[net].b3 + e);
+#pragma unroll
+        for (int it = 0; it < W2_IT; it++) {
+            const int e = tid + it * nthreads;
+            if (e < 2 * 64 * 8) store8<FMT>(sm + L.w2[e >> 9] + act_chunk_off((e >> 3) & 63, e & 7), v[it]);
+        }
+    }
+    {   // fp32 small parameters: P1 = {W1 row, b1, 0..} [64][8], b2 [64], W3 [k3][64], b3 [k3] per net, one flat task list
+        const int S1 = 2 * 512, S2 = S1 + 128, S3 = S2 + 64 * (K + 1), S4 = S3 + (K + 1);
+        for (int e0 = tid; e0 < S4; e0 += 4 * nthreads) {
+            float v[4];
+            float* dst[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int e = e0 + u * nthreads;
+                dst[u] = nullptr;
+                v[u] = 0.0f;
+                if (e >= S4) continue;
+                const float* src = nullptr;
+                if (e < S1) {
+                    const int net = e >> 9, j = (e >> 3) & 63, i = e & 7;
+                    dst[u] = reinterpret_cast<float*>(sm + L.p1[net]) + (e & 511);
+                    if (i < O) src = a.params + offs[net].W1 + j * O + i;
+                    else if (i == O) src = a.params + offs[net].b1 + j;
+                } else if (e < S2) {
+                    const int t = e - S1, net = t >> 6;
+                    dst[u] = reinterpret_cast<float*>(sm + L.b2[net]) + (t & 63);
+                    src = a.params + offs[net].b2 + (t & 63);
+                } else if (e < S3) {
+                    const int t = e - S2, net = t < 64 * K ? 0 : 1, idx = net ? t - 64 * K : t;
+                    dst[u] = reinterpret_cast<float*>(sm + L.w3[net]) + idx;
+                    src = a.params + offs[net].W3 + idx;
+                } else {
+                    const int t = e - S3, net = t < K ? 0 : 1, idx = net ? t - K : t;
+                    dst[u] = reinterpret_cast<float*>(sm + L.b3p[net]) + idx;
+                    src = a.params + offs[net].b3 + idx;
+                }
+                if (src) v[u] = __ldg(src);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                if (dst[u]) *dst[u] = v[u];
+        }
     }
     fence_async_smem();
     tc_fence_before();
@@ -251,10 +255,7 @@ __global__ void __launch_bounds__(NWG * 128 + 32, 1) update_tc_kernel(const UpdA
 
     RowSums rs;
     float gb3c = 0.0f;  // critic output-bias gradient partial of this thread
-    if (issuer_warp) {
-        if (lane == 0) tc_issuer<FMT, NWG>(sm, L, bars, tmem, K, ntiles);
-        __syncwarp();
-    } else {
+    {
         // ---------------- compute warpgroup ------------------------------------------------------------------
         const int g = warp >> 2, wt = tid & 127, w4 = warp & 3;
         uint8_t* wg = sm + L.wg0 + g * L.wg_stride;
@@ -262,7 +263,25 @@ __global__ void __launch_bounds__(NWG * 128 + 32, 1) update_tc_kernel(const UpdA
         float* x = reinterpret_cast<float*>(wg + L.lg) + wt * L.ldo;     // this row's logits / dL/dlogits
         float* b3acc = reinterpret_cast<float*>(wg + L.b3) + wt * L.ldo; // this thread's actor db3 partials
         for (int q = 0; q < K; q++) b3acc[q] = 0.0f;
-        uint64_t *ready = bars + g, *doneZ = bars + NWG + g, *doneW = bars + 2 * NWG + g;
+        uint64_t *doneZ = bars + NWG + g, *doneW = bars + 2 * NWG + g;
+        WgDescs D;
+        {
+            const uint32_t wb = smem_u32(wg);
+            D.a1k = act_desc_kmajor(wb + L.a1, 0); D.a1m = act_desc_mnmajor(wb + L.a1, 0);
+            D.a2m = act_desc_mnmajor(wb + L.a2, 0);
+            D.a3k = act_desc_kmajor(wb + L.a3, 0); D.a3m = act_desc_mnmajor(wb + L.a3, 0);
+            D.xe = narrow_desc_mnmajor(wb + L.xe, TC_ROWS, 0); D.dout = narrow_desc_mnmajor(wb + L.dout, TC_ROWS, 0);
+            for (int n = 0; n < 2; n++) {
+                D.w2k[n] = act_desc_kmajor(smem_u32(sm) + L.w2[n], 0);
+                D.w2m[n] = act_desc_mnmajor(smem_u32(sm) + L.w2[n], 0);
+                D.c[n] = tc_cols(NWG, g, n, L.n3a);
+            }
+            D.Z = tmem + (uint32_t)g * 64u;
+            D.id_w3[0] = idesc_f16(FMT, 64, L.n3a, 1, 1);
+            D.id_w3[1] = idesc_f16(FMT, 64, 8, 1, 1);
+            D.fresh = 0xFFu;
+        }
+        const int barid = 1 + g;
         uint32_t pz = 0, pw = 0;
         bool pendingW = false;
         const uint32_t zaddr = tmem_addr(tmem, (uint32_t)w4 * 32u, (uint32_t)g * 64u);
@@ -272,23 +291,55 @@ __global__ void __launch_bounds__(NWG * 128 + 32, 1) update_tc_kernel(const UpdA
         if (a.hp.norm_adv) { meanf = a.adv_stats[0]; stdf = a.adv_stats[1]; }
         const int nwg_total = gridDim.x * NWG;
 
-        for (int tile = blockIdx.x * NWG + g; tile < ntiles; tile += nwg_total) {
+        // per-row inputs of a tile, gathered through the permutation one tile ahead (the loads of tile t+1 fly while
+        // tile t computes)
+        struct RowIn {
+            int64_t r;
+            float o[4];      // obs (O <= 4: prefetched; wider observations are loaded at use)
+            float old_logp, adv, ret, old_val;
+            bool on;
+        };
+        auto gather = [&](int tile) {
+            RowIn in;
             const int rloc = tile * TC_ROWS + wt;
-            const bool on = rloc < a.mb_size;
-            int64_t r = 0;
+            in.on = tile < ntiles && rloc < a.mb_size;
+            in.r = 0;
+            in.o[0] = in.o[1] = in.o[2] = in.o[3] = 0.0f;
+            in.old_logp = in.adv = in.ret = in.old_val = 0.0f;
+            if (in.on) {
+                const int64_t r = a.perm ? (int64_t)__ldg(a.perm + a.mb_start + rloc) : a.mb_start + rloc;
+                in.r = r;
+                if (O == 4) {
+                    const float4 o4 = __ldg(reinterpret_cast<const float4*>(a.obs + r * 4));
+                    in.o[0] = o4.x; in.o[1] = o4.y; in.o[2] = o4.z; in.o[3] = o4.w;
+                } else if (O < 4) {
+#pragma unroll
+                    for (int i = 0; i < 3; i++)
+                        if (i < O) in.o[i] = __ldg(a.obs + r * O + i);
+                }
+                in.old_logp = __ldg(a.old_logprob + r);
+                in.adv = __ldg(a.adv + r);
+                in.ret = __ldg(a.ret + r);
+                if (a.hp.clip_vloss) in.old_val = __ldg(a.old_val + r);
+            }
+            return in;
+        };
+        RowIn nxt = gather(blockIdx.x * NWG + g);
+        for (int tile = blockIdx.x * NWG + g; tile < ntiles; tile += nwg_total) {
+            const RowIn cur = nxt;
+            nxt = gather(tile + nwg_total);
+            const bool on = cur.on;
+            const int64_t r = cur.r;
             float xe[8];
 #pragma unroll
             for (int i = 0; i < 8; i++) xe[i] = 0.0f;
-            if (on) {
-                r = a.perm ? (int64_t)a.perm[a.mb_start + rloc] : a.mb_start + rloc;
-                if (O == 4) {
-                    const float4 o4 = __ldg(reinterpret_cast<const float4*>(a.obs + r * 4));
-                    xe[0] = o4.x; xe[1] = o4.y; xe[2] = o4.z; xe[3] = o4.w;
-                } else {
+            if (O <= 4) {
 #pragma unroll
-                    for (int i = 0; i < 7; i++)
-                        if (i < O) xe[i] = __ldg(a.obs + r * O + i);
-                }
+                for (int i = 0; i < 4; i++) xe[i] = cur.o[i];
+            } else if (on) {
+#pragma unroll
+                for (int i = 0; i < 7; i++)
+                    if (i < O) xe[i] = __ldg(a.obs + r * O + i);
             }
 #pragma unroll
             for (int i = 0; i < 8; i++)
@@ -312,7 +363,8 @@ __global__ void __launch_bounds__(NWG * 128 + 32, 1) update_tc_kernel(const UpdA
                     store8<FMT>(A1 + act_chunk_off(wt, c), h);
                 }
                 fence_async_smem();
-                mbar_arrive(ready);
+                bar_sync(barid, 128);
+                if (wt == 0) issue_stage<FMT, 0>(D, net, tmem, doneZ, doneW);
                 mbar_wait(doneZ, pz); pz ^= 1u;
                 tc_fence_after();
                 // ---- S2: h2 = tanh(Z + b2) -> A2; output layer; loss; dOut -> DO
@@ -342,8 +394,8 @@ __global__ void __launch_bounds__(NWG * 128 + 32, 1) update_tc_kernel(const UpdA
                 if (net == 0) {
                     if (on) {
                         const uint64_t mbits = masked ? pack_mask(a.mask + r * K, K) : ~0ull;
-                        actor_row_loss(x, a.d, masked, mbits, a.actions + r * heads, __ldg(a.old_logprob + r),
-                                       __ldg(a.adv + r), a.hp, meanf, stdf, 1.0f, rs);
+                        actor_row_loss(x, a.d, masked, mbits, a.actions + r * heads, cur.old_logp, cur.adv, a.hp, meanf, stdf,
+                                       1.0f, rs);
                         for (int q = 0; q < K; q++) b3acc[q] += x[q];
                     } else {
                         for (int q = 0; q < K; q++) x[q] = 0.0f;
@@ -355,16 +407,15 @@ __global__ void __launch_bounds__(NWG * 128 + 32, 1) update_tc_kernel(const UpdA
                         store8<FMT>(DO + c * (TC_ROWS * 16) + wt * 16, v);
                     }
                 } else {
-                    gv = on ? critic_row_loss(gv, __ldg(a.ret + r), a.hp.clip_vloss ? __ldg(a.old_val + r) : 0.0f, a.hp,
-                                              1.0f, rs)
-                            : 0.0f;
+                    gv = on ? critic_row_loss(gv, cur.ret, cur.old_val, a.hp, 1.0f, rs) : 0.0f;
                     gb3c += gv;
                     float v[8] = {gv, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                     store8<FMT>(DO + wt * 16, v);
                 }
                 tc_fence_before();
                 fence_async_smem();
-                mbar_arrive(ready);
+                bar_sync(barid, 128);
+                if (wt == 0) issue_stage<FMT, 1>(D, net, tmem, doneZ, doneW);
                 // ---- S3: dZ2 = (dOut W3) * (1 - h2^2) -> A3
                 float d[64];
 #pragma unroll
@@ -384,7 +435,8 @@ __global__ void __launch_bounds__(NWG * 128 + 32, 1) update_tc_kernel(const UpdA
 #pragma unroll
                 for (int c = 0; c < 8; c++) store8<FMT>(A3 + act_chunk_off(wt, c), d + c * 8);
                 fence_async_smem();
-                mbar_arrive(ready);
+                bar_sync(barid, 128);
+                if (wt == 0) issue_stage<FMT, 2>(D, net, tmem, doneZ, doneW);
                 mbar_wait(doneZ, pz); pz ^= 1u;
                 tc_fence_after();
                 // ---- S4: dZ1 = Z * (1 - h1^2) -> A2 (h2's buffer; G5 is done with it)
@@ -402,7 +454,8 @@ __global__ void __launch_bounds__(NWG * 128 + 32, 1) update_tc_kernel(const UpdA
                 mbar_wait(doneW, pw); pw ^= 1u;  // G3 has read A1 / A3 (keeps doneW in lock-step)
                 tc_fence_before();
                 fence_async_smem();
-                mbar_arrive(ready);
+                bar_sync(barid, 128);
+                if (wt == 0) issue_stage<FMT, 3>(D, net, tmem, doneZ, doneW);
                 pendingW = true;
             }
         }
@@ -492,32 +545,40 @@ __global__ void __launch_bounds__(NWG * 128 + 32, 1) update_tc_kernel(const UpdA
     constexpr int NT = NWG * 128;
     double* red = reinterpret_cast<double*>(sm + L.wg0);                    // [5][NT]   (A1/A2 of warpgroup 0)
     float* gbc = reinterpret_cast<float*>(sm + L.wg0 + 5 * NT * 8);         // [NT]
-    if (!issuer_warp) {
+    {
         red[0 * NT + tid] = rs.pg; red[1 * NT + tid] = rs.v; red[2 * NT + tid] = rs.ent;
         red[3 * NT + tid] = rs.kl; red[4 * NT + tid] = rs.clip;
         gbc[tid] = gb3c;
     }
     __syncthreads();
-    if (tid < 5) {
+    // one warp per quantity: lane-strided partial sums, then a fixed xor tree (deterministic)
+    if (warp < 5) {
         double acc = 0.0;
-        for (int m = 0; m < NT; m++) acc += red[tid * NT + m];
-        a.dpart[(size_t)blockIdx.x * UPD_NDIAG + tid] = acc;
-    } else if (tid >= 32 && tid < 32 + K) {
-        const int q = tid - 32;
+        for (int m = lane; m < NT; m += 32) acc += red[warp * NT + m];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) a.dpart[(size_t)blockIdx.x * UPD_NDIAG + warp] = acc;
+    } else if (warp == 5) {
         float acc = 0.0f;
-        for (int g = 0; g < NWG; g++) {
-            const float* b = reinterpret_cast<const float*>(sm + L.wg0 + g * L.wg_stride + L.b3);
-            for (int m = 0; m < TC_ROWS; m++) acc += b[m * L.ldo + q];
+        for (int m = lane; m < NT; m += 32) acc += gbc[m];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) slab[offs[1].b3] = acc * sc;
+    } else {
+        for (int q = warp - 6; q < K; q += NWG * 4 - 6) {
+            float acc = 0.0f;
+            for (int g = 0; g < NWG; g++) {
+                const float* b = reinterpret_cast<const float*>(sm + L.wg0 + g * L.wg_stride + L.b3);
+                for (int m = lane; m < TC_ROWS; m += 32) acc += b[m * L.ldo + q];
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0) slab[offs[0].b3 + q] = acc * sc;
         }
-        slab[offs[0].b3 + q] = acc * sc;
-    } else if (tid == 96) {
-        float acc = 0.0f;
-        for (int m = 0; m < NT; m++) acc += gbc[m];
-        slab[offs[1].b3] = acc * sc;
     }
     tc_fence_before();
     __syncthreads();
-    if (issuer_warp) tmem_dealloc(tmem, 512);
+    if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
 template <int FMT, int NWG>
@@ -535,7 +596,7 @@ static int launch_tc(const UpdArgs& a, int* grid_out, cudaStream_t st) {
     int grid = (ntiles + NWG - 1) / NWG;
     if (grid > sms) grid = sms;
     if (grid > UPD_MAX_GRID) grid = UPD_MAX_GRID;
-    update_tc_kernel<FMT, NWG><<<grid, NWG * 128 + 32, smem, st>>>(a);
+    update_tc_kernel<FMT, NWG><<<grid, NWG * 128, smem, st>>>(a);
     PPO_LAUNCH_CHECK();
     *grid_out = grid;
     return PPO_OK;

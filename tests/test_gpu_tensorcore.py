@@ -24,10 +24,10 @@ def round16(a, fmt):
     return t.to(torch.float16 if fmt == 0 else torch.bfloat16).to(torch.float64).numpy()
 
 
-def lanes_m64(img):
+def lanes_m64(img, lane0=0):
     """rows of an M = 64 accumulator inside the [128 lanes][64 cols] tensor-memory image"""
     m = np.arange(64)
-    return img[(m % 16) + 32 * (m // 16)]
+    return img[lane0 + (m % 16) + 32 * (m // 16)]
 
 
 def run_probe(P, mode, fmt, A, B):
@@ -45,13 +45,15 @@ def run_probe(P, mode, fmt, A, B):
         return a @ b, img
     if mode == 2:
         return a.T @ b, lanes_m64(img)
+    if mode == 4:
+        return a.T @ b, lanes_m64(img, 16)
     return a.T @ b, lanes_m64(img)[:, :16]
 
 
-PROBE_B_SHAPE = {0: (64, 64), 1: (64, 64), 2: (128, 64), 3: (128, 16)}
+PROBE_B_SHAPE = {0: (64, 64), 1: (64, 64), 2: (128, 64), 3: (128, 16), 4: (128, 64)}
 
 
-@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
 @pytest.mark.parametrize("fmt", [0, 1])
 def test_umma_probe(P, mode, fmt):
     rng = np.random.default_rng(100 * mode + fmt)

@@ -11,7 +11,7 @@ import ppo_libtorch_b200 as P  # noqa: E402
 from test_gpu_tensorcore import PROBE_B_SHAPE, run_probe  # noqa: E402
 
 for fmt in (0, 1):
-    for mode in range(4):
+    for mode in range(5):
         rng = np.random.default_rng(mode)
         A = rng.standard_normal((128, 64)).astype(np.float32)
         B = rng.standard_normal(PROBE_B_SHAPE[mode]).astype(np.float32)
