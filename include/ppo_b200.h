@@ -308,6 +308,9 @@ int ppo_trainer_set_comm(ppo_trainer* t, ppo_comm* comm);
 int ppo_debug_umma_probe(int mode, int fmt, const float* A, const float* B, float* D, ppo_stream_t stream);
 /* Same GEMM issued `reps` times back to back by one thread; d_cycles[0] (device int64) = SM clocks from the first issue
  * to the completion of the last (how fast the tensor pipe retires each operand layout). */
+/* In-kernel timeline of the tensor-core update kernel: d_ts = device buffer of 256 int64 (NULL switches it off);
+ * later launches stamp the SM clock of CTA 0, thread `who` at fixed points (tools/tc_timeline.py prints them). */
+int ppo_debug_tc_timeline(long long* d_ts, int who);
 int ppo_debug_umma_time(int mode, int fmt, const float* A, const float* B, float* D, int reps, long long* d_cycles,
                         ppo_stream_t stream);
 

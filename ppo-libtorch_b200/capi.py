@@ -124,6 +124,7 @@ _PROTOS = {
     "ppo_comm_allreduce_f32": (C.c_int, [_P, _P, C.c_int64, _P]),
     "ppo_comm_allreduce_f64": (C.c_int, [_P, _P, C.c_int64, _P]),
     "ppo_debug_umma_probe": (C.c_int, [C.c_int, C.c_int, _P, _P, _P, _P]),
+    "ppo_debug_tc_timeline": (C.c_int, [_P, C.c_int]),
     "ppo_debug_umma_time": (C.c_int, [C.c_int, C.c_int, _P, _P, _P, C.c_int, _P, _P]),
 }
 EXPORTS = sorted(_PROTOS)

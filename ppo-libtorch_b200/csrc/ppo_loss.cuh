@@ -7,16 +7,20 @@
 
 namespace ppo {
 
-struct RowSums {  // per-thread partial sums of the minibatch diagnostics
-    double pg = 0.0, v = 0.0, ent = 0.0, kl = 0.0, clip = 0.0;
+template <class T>
+struct RowSumsT {  // per-thread partial sums of the minibatch diagnostics
+    T pg = 0, v = 0, ent = 0, kl = 0, clip = 0;
 };
+using RowSums = RowSumsT<double>;   // fp32 FMA path: double like the oracle; the tensor-core path sums a few dozen rows
+using RowSumsF = RowSumsT<float>;   // per thread in float and switches to double in the cross-thread reduction
 
 // Actor side of one sample.  x[0..K) holds the logits on entry and dL/dlogits * (1/scale_inv) on exit:
 // every gradient is multiplied by `gscale` (1/n for the FMA path, 1 for the tensor-core path, which applies
 // 1/n once when the accumulators are drained).
+template <class T>
 __device__ inline void actor_row_loss(float* x, const Dims& d, bool masked, uint64_t mbits, const int32_t* act,
                                       float old_logp, float adv_raw, const ppo_hyper& hp, float meanf, float stdf,
-                                      float gscale, RowSums& s) {
+                                      float gscale, RowSumsT<T>& s) {
     const int heads = d.heads;
     const float c = hp.clip_coef, lo = 1.0f - c, hi = 1.0f + c;
     // pass 1: log-prob of the stored actions + entropy, summed over heads (Agent.cpp:168)
@@ -36,14 +40,14 @@ __device__ inline void actor_row_loss(float* x, const Dims& d, bool masked, uint
     }
     const float logratio = newlogp - old_logp;                      // :585
     const float ratio = expf(logratio);                             // :586
-    s.kl += (double)((ratio - 1.0f) - logratio);                    // :352
-    if (fabsf(ratio - 1.0f) > c) s.clip += 1.0;                     // :348
+    s.kl += (T)((ratio - 1.0f) - logratio);                         // :352
+    if (fabsf(ratio - 1.0f) > c) s.clip += (T)1;                    // :348
     float A = adv_raw;
     if (hp.norm_adv) A = __fdiv_rn(A - meanf, stdf + 1e-8f);        // :591-594
     const float rc = ratio < lo ? lo : (ratio > hi ? hi : ratio);
     const float pg1 = -A * ratio, pg2 = -A * rc;                    // :597-598
-    s.pg += (double)(pg1 > pg2 ? pg1 : pg2);
-    s.ent += (double)ent;
+    s.pg += (T)(pg1 > pg2 ? pg1 : pg2);
+    s.ent += (T)ent;
     // d pg / d ratio: ATen max splits ties 1/2-1/2, clamp's mask is inclusive (SURVEY §8 a-bis)
     float dpg_dr;
     if (ratio >= lo && ratio <= hi) dpg_dr = -A;
@@ -72,8 +76,9 @@ __device__ inline void actor_row_loss(float* x, const Dims& d, bool masked, uint
 }
 
 // Critic side of one sample: accumulates the (un-halved) value-loss term, returns dL/dvalue * gscale.
+template <class T>
 __device__ inline float critic_row_loss(float value, float R, float vo, const ppo_hyper& hp, float gscale,
-                                        RowSums& s) {
+                                        RowSumsT<T>& s) {
     const float c = hp.clip_coef;
     const float du = value - R;
     const float u = du * du;
@@ -83,14 +88,61 @@ __device__ inline float critic_row_loss(float value, float R, float vo, const pp
         const float dcl = dvo < -c ? -c : (dvo > c ? c : dvo);
         const float vc = vo + dcl;
         const float w = (vc - R) * (vc - R);
-        s.v += (double)(u > w ? u : w);
+        s.v += (T)(u > w ? u : w);
         const float dw = (dvo >= -c && dvo <= c) ? (vc - R) : 0.0f;
         dv = (u > w) ? du : ((w > u) ? dw : 0.5f * du + 0.5f * dw);
     } else {  // :621-625
-        s.v += (double)u;
+        s.v += (T)u;
         dv = du;
     }
     return hp.vf_coef * gscale * dv;
+}
+
+// Single unmasked head (PPO_Discrete) with the fast-math intrinsics: the tensor-core path's forward values carry
+// ~1e-3 relative error already, so __expf / __logf / __fdividef (2 ulp-class) change nothing measurable, and the
+// whole row is one short dependent chain instead of ~10 libm-grade calls.  Same formulas as actor_row_loss.
+__device__ inline void actor_row_loss_fast1(float* x, int K, int aa, float old_logp, float adv_raw, const ppo_hyper& hp,
+                                            float meanf, float stdf, RowSumsF& s) {
+    const float c = hp.clip_coef, lo = 1.0f - c, hi = 1.0f + c;
+    float mx = x[0];
+    for (int j = 1; j < K; j++) mx = fmaxf(mx, x[j]);
+    float sum = 0.0f;
+    for (int j = 0; j < K; j++) sum += __expf(x[j] - mx);
+    const float lse = mx + __logf(sum), rs = __fdividef(1.0f, sum);
+    const float newlogp = x[aa] - lse;
+    const bool exact = hp.entropy_mode == PPO_ENTROPY_EXACT;
+    float ent = 0.0f;
+    if (exact) {
+        for (int j = 0; j < K; j++) {
+            const float lp = x[j] - lse, p = __expf(x[j] - mx) * rs;
+            if (p > 0.0f) ent -= lp * p;
+        }
+    } else {
+        ent = -FLT_MIN;   // Categorical.cpp:114-117: every log-prob clamps up to FLT_MIN, sum(p) = 1
+    }
+    const float logratio = newlogp - old_logp;
+    const float ratio = __expf(logratio);
+    s.kl += (ratio - 1.0f) - logratio;
+    if (fabsf(ratio - 1.0f) > c) s.clip += 1.0f;
+    float A = adv_raw;
+    if (hp.norm_adv) A = __fdividef(A - meanf, stdf + 1e-8f);
+    const float rc = ratio < lo ? lo : (ratio > hi ? hi : ratio);
+    const float pg1 = -A * ratio, pg2 = -A * rc;
+    s.pg += pg1 > pg2 ? pg1 : pg2;
+    s.ent += ent;
+    float dpg_dr;
+    if (ratio >= lo && ratio <= hi) dpg_dr = -A;
+    else if (pg1 > pg2) dpg_dr = -A;
+    else if (pg1 == pg2) dpg_dr = -0.5f * A;
+    else dpg_dr = 0.0f;
+    const float g_logp = dpg_dr * ratio;
+    const float ge = hp.ent_coef;
+    for (int j = 0; j < K; j++) {
+        const float p = __expf(x[j] - mx) * rs;
+        float dz = g_logp * ((j == aa ? 1.0f : 0.0f) - p);
+        if (exact && ge != 0.0f && p > 0.0f) dz += ge * p * ((x[j] - lse) + ent);
+        x[j] = dz;
+    }
 }
 
 }  // namespace ppo

@@ -6,20 +6,21 @@
 // fp32 accumulation in tensor memory); everything per-sample (layer 1, bias + tanh, the output layer, softmax /
 // ratio / clipping / value loss, the tanh derivatives) runs one-thread-per-row on the CUDA cores.
 //
-// CTA = NWG warpgroups (128 threads = 128 minibatch rows each).  A warpgroup walks its 128-row tiles; per tile and
-// net it writes four operand stages to shared memory, and after a warpgroup-wide named barrier its thread 0 issues
-// the stage's MMAs (measured: one issuer warp serving all warpgroups was itself the bottleneck, ~1100 dependent
-// instructions per tile).  Completions come back through two mbarriers per warpgroup ("doneZ": an accumulator it must
-// read; "doneW": operands it may overwrite):
-//   S1  h1 = tanh([x,1] P1^T)            -> A1          G1 : Z   = A1 W2^T                        (doneZ)
-//   S2  h2 = tanh(Z + b2) -> A2, logits/value, loss, dOut -> DO
-//                                                        G5 : dW3^T += A2^T DO                     (doneW)
-//   S3  dZ2 = (dOut W3) (1 - h2^2)       -> A3          G2 : Z   = A3 W2                          (doneZ)
-//                                                        G3 : dW2 += A3^T A1 ; d[.|b2] += A3^T XE   (doneW)
-//   S4  dZ1 = Z (1 - h1^2)               -> A2          G4 : d[W1|b1] += A2^T XE                  (doneW)
-// While one warpgroup waits on the tensor core another computes, so the two pipes overlap without a software
-// pipeline inside a warpgroup.  All weight-gradient accumulators stay in tensor memory for the whole kernel (private
-// to a warpgroup, one issuing thread each => in-order accumulation) and are drained once into the CTA's slab; reduce_kernel (update.cu) sums
+// CTA = NWG warpgroups (128 threads = 128 minibatch rows each).  A warpgroup walks its 128-row tiles; per tile it
+// runs four phases, each over BOTH nets (actor, then critic), so that while the tensor core works on one net's
+// stage the same threads compute the other net's (the nets are independent graphs) — a tensor round trip is
+// ~800 cycles, measured, and four of them per net were the critical path before the nets were interleaved:
+//   P1  h1 = tanh([x,1] P1^T)               -> A1[net]      G1 : Z[net] = A1 W2^T                      (doneZ)
+//   P2  h2 = tanh(Z + b2) -> A2[net], logits / value, loss, dOut -> DO[net]
+//                                                            G5 : dW3^T += A2^T DO                      (doneW)
+//   P3  dZ2 = (dOut W3)(1 - h2^2)           -> A2[net]      G2 : Z[net] = A2 W2                        (doneZ)
+//                                                            G3 : dW2 += A2^T A1 ; d[.|b2] += A2^T XE   (doneW)
+//   P4  dZ1 = Z (1 - h1^2)                  -> A2[net]      G4 : d[W1|b1] += A2^T XE                   (doneW)
+// After a phase's shared-memory writes and a warpgroup-wide named barrier, thread 0 of the warpgroup issues the
+// MMAs (one issuer warp for the whole CTA was measured to be a bottleneck).  Completions come back through two
+// mbarriers per (warpgroup, net): "doneZ" (an accumulator to read) and "doneW" (operands free to overwrite).
+// All weight-gradient accumulators stay in tensor memory for the whole kernel, private to a warpgroup (one issuing
+// thread each => fixed accumulation order) and are drained once into the CTA's slab; reduce_kernel (update.cu) sums
 // the slabs in fixed order, so results are run-to-run identical.  Gradients are kept un-normalised (no 1/n) until
 // the drain so that fp16 operands do not underflow.
 #include "ppo_loss.cuh"
@@ -31,13 +32,13 @@ using namespace umma;
 
 constexpr int TC_H = 64;
 constexpr int TC_ROWS = 128;        // rows per warpgroup tile
-constexpr int TC_MAX_K = 24;        // sum of logits: 2 x (168 + pad8(K)) + 128 tensor-memory columns must fit in 512
+constexpr int TC_MAX_K = 21;        // sum of logits (shared-memory budget of the per-row logit / db3 scratch)
 constexpr int ACT_BYTES = TC_ROWS * 128;  // one activation tile
 
 struct TcLayout {   // byte offsets into the 1024-aligned dynamic shared memory
-    int w2[2];      // bf16/fp16 W2 of actor (0) and critic (1), 64 rows x 128 B each
+    int w2[2];      // 16-bit W2 of actor (0) and critic (1), 64 rows x 128 B each
     int wg0, wg_stride;                  // per-warpgroup block
-    int a1, a2, a3, xe, dout, lg, b3;    // offsets inside a warpgroup block
+    int a1[2], a2[2], xe[2], dout[2], lg, b3;   // offsets inside a warpgroup block ([net], XE: [tile parity])
     int p1[2], b2[2], w3[2], b3p[2];     // fp32 small parameters per net
     int bars, tmem_slot, end;
     int ldo, n3a;                        // logits row stride (floats), padded actor logit count
@@ -48,12 +49,11 @@ __host__ __device__ inline TcLayout tc_layout(int K, int nwg) {
     L.n3a = (K + 7) & ~7;
     L.w2[0] = 0;
     L.w2[1] = 8192;
-    L.a1 = 0;
-    L.a2 = ACT_BYTES;
-    L.a3 = 2 * ACT_BYTES;
-    L.xe = 3 * ACT_BYTES;
-    L.dout = L.xe + TC_ROWS * 16;
-    L.lg = L.dout + (L.n3a / 8) * TC_ROWS * 16;
+    L.a1[0] = 0; L.a1[1] = ACT_BYTES; L.a2[0] = 2 * ACT_BYTES; L.a2[1] = 3 * ACT_BYTES;
+    L.xe[0] = 4 * ACT_BYTES; L.xe[1] = L.xe[0] + TC_ROWS * 16;
+    L.dout[0] = L.xe[1] + TC_ROWS * 16;
+    L.dout[1] = L.dout[0] + (L.n3a / 8) * TC_ROWS * 16;
+    L.lg = L.dout[1] + TC_ROWS * 16;
     L.b3 = L.lg + ((TC_ROWS * L.ldo * 4 + 15) & ~15);
     L.wg_stride = (L.b3 + ((TC_ROWS * L.ldo * 4 + 15) & ~15) + 1023) & ~1023;
     L.wg0 = 16384;
@@ -65,11 +65,19 @@ __host__ __device__ inline TcLayout tc_layout(int K, int nwg) {
         L.w3[n] = o; o += k3 * TC_H * 4;
         L.b3p[n] = o; o += ((k3 + 3) & ~3) * 4;
     }
-    L.bars = o; o += 3 * 4 * 8;
+    L.bars = o; o += 4 * 4 * 8;
     L.tmem_slot = o; o += 16;
     L.end = o;
     return L;
 }
+
+// optional in-kernel timeline (ppo_debug_tc_timeline): SM clock stamps of CTA 0, thread `who`, slot-indexed
+__device__ long long* g_tc_ts = nullptr;
+__device__ int g_tc_ts_who = 0;
+#define TC_TS(slot)                                                                       \
+    do {                                                                                  \
+        if (ts_buf && (slot) < 256) ts_buf[(slot)] = clock64();                           \
+    } while (0)
 
 __device__ __forceinline__ float tanh_fast(float x) {
     float y;
@@ -90,78 +98,102 @@ __device__ __forceinline__ void load8(const uint8_t* src, float* v) {
     v[4] = unpack_lo<FMT>(u.z); v[5] = unpack_hi<FMT>(u.z); v[6] = unpack_lo<FMT>(u.w); v[7] = unpack_hi<FMT>(u.w);
 }
 
-// tensor-memory column map: Z of warpgroup g at 64 g; then one block of gradient accumulators (M = 64 layout) PER
-// warpgroup, so that every accumulator sees its MMAs in a fixed order (run-to-run identical sums):
-//   actor {dW2 64, d[.|b2] 8, d[W1|b1] 8, dW3^T n3a}, critic {64, 8, 8, 8}  =>  168 + n3a columns per warpgroup
+// tensor-memory map: Z[g][net] at columns 64 (2 g + net) (M = 128: all lanes); then one block of gradient
+// accumulators PER warpgroup (fixed accumulation order => run-to-run identical sums), M = 64 layout, the actor's in
+// the lower half of every 32-lane subpartition and the critic's in the upper half (lane + 16):
+//   {dW2 64, d[.|b2] 8, d[W1|b1] 8, dW3^T n3a}  =>  80 + n3a columns per warpgroup
 struct TcCols {
-    uint32_t w2, xe2, xe1, w3;
+    uint32_t w2, xe2, xe1, w3;   // tensor-memory address offsets (lane << 16 | column)
 };
 __device__ __forceinline__ TcCols tc_cols(int nwg, int g, int net, int n3a) {
-    const uint32_t base = (uint32_t)nwg * 64u + (uint32_t)g * (168u + (uint32_t)n3a) + (net == 0 ? 0u : 80u + (uint32_t)n3a);
+    const uint32_t base = (uint32_t)nwg * 128u + (uint32_t)g * (80u + (uint32_t)n3a) + (net ? (16u << 16) : 0u);
     return TcCols{base, base + 64u, base + 72u, base + 80u};
 }
 
-// ---- MMA issue: thread 0 of a warpgroup issues that warpgroup's stage (its accumulators are private, so no ordering
-// between the issuing threads of different warpgroups is needed).  Descriptors are precomputed; a K-step only adds a
-// constant to the start-address field (16-byte units).
-struct WgDescs {
-    uint64_t a1k, a1m, a2m, a3k, a3m, xe, dout;  // activation tiles (K-major / MN-major views), narrow tiles
-    uint64_t w2k[2], w2m[2];                      // W2 of actor / critic
-    uint32_t Z;                                   // tensor-memory address of this warpgroup's Z block
-    TcCols c[2];
-    uint32_t id_w3[2];
-    uint32_t fresh;                               // bit (net * 4 + accumulator): next MMA into it must overwrite
+// ---- MMA issue: warp 0 of a warpgroup issues that warpgroup's stage.  The whole warp walks the code with
+// warp-uniform operands (every input is broadcast from lane 0 with a shuffle, which lets the compiler keep the
+// descriptors in uniform registers instead of converting per-thread registers before every tcgen05.mma — that
+// conversion chain made one MMA cost ~120 issue cycles); one elected lane executes the instructions.
+struct WgIssue {
+    uint32_t wb, sb, tmem;    // shared-memory address of the warpgroup block / of the CTA block, tensor-memory base
+    int g;
+    uint32_t fresh;           // bit (net * 4 + accumulator): the next MMA into it must overwrite
 };
-template <int FMT, int ST>
-__device__ __forceinline__ void issue_stage(WgDescs& d, int net, uint32_t tmem, uint64_t* doneZ, uint64_t* doneW) {
+template <int FMT, int NWG, int ST>
+__device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int net_, int par_, uint64_t* doneZ,
+                                            uint64_t* doneW) {
     constexpr uint32_t id_fwd = idesc_f16(FMT, 128, 64, 0, 0);   // Z = A1 W2^T
-    constexpr uint32_t id_dx = idesc_f16(FMT, 128, 64, 0, 1);    // Z = A3 W2
-    constexpr uint32_t id_dw = idesc_f16(FMT, 64, 64, 1, 1);     // dW2 += A3^T A1
+    constexpr uint32_t id_dx = idesc_f16(FMT, 128, 64, 0, 1);    // Z = A2 W2
+    constexpr uint32_t id_dw = idesc_f16(FMT, 64, 64, 1, 1);     // dW2 += A2^T A1
     constexpr uint32_t id_n8 = idesc_f16(FMT, 64, 8, 1, 1);      // skinny, N = 8
+    const uint32_t wb = __shfl_sync(0xffffffffu, w.wb, 0), sb = __shfl_sync(0xffffffffu, w.sb, 0);
+    const uint32_t tmem = __shfl_sync(0xffffffffu, w.tmem, 0);
+    const int g = __shfl_sync(0xffffffffu, w.g, 0), net = __shfl_sync(0xffffffffu, net_, 0);
+    const int par = __shfl_sync(0xffffffffu, par_, 0);
+    const uint32_t fresh = __shfl_sync(0xffffffffu, w.fresh, 0);
     const uint32_t fb = (uint32_t)net * 4u;
-    const TcCols c = d.c[net];
+    const TcCols c = tc_cols(NWG, g, net, L.n3a);
+    const uint32_t Z = tmem + (uint32_t)(g * 2 + net) * 64u;
+    const uint32_t A1 = wb + L.a1[net], A2 = wb + L.a2[net], W2 = sb + L.w2[net];
     tc_fence_after();
+    const bool lead = elect_one();
     if (ST == 0) {
+        const uint64_t da = act_desc_kmajor(A1, 0), db = act_desc_kmajor(W2, 0);
+        if (lead) {
 #pragma unroll
-        for (int ks = 0; ks < 4; ks++) mma_f16(d.Z, d.a1k + 2u * ks, d.w2k[net] + 2u * ks, id_fwd, ks > 0);
-        mma_commit(doneZ);
-    } else if (ST == 1) {
-        const uint32_t acc0 = (d.fresh >> (fb + 3)) & 1u ? 0u : 1u;
-#pragma unroll
-        for (int ks = 0; ks < 8; ks++)
-            mma_f16(tmem + c.w3, d.a2m + 128u * ks, d.dout + 16u * ks, d.id_w3[net], ks > 0 ? 1u : acc0);
-        d.fresh &= ~(1u << (fb + 3));
-        mma_commit(doneW);
-    } else if (ST == 2) {
-#pragma unroll
-        for (int ks = 0; ks < 4; ks++) mma_f16(d.Z, d.a3k + 2u * ks, d.w2m[net] + 128u * ks, id_dx, ks > 0);
-        mma_commit(doneZ);
-        const uint32_t acc0 = (d.fresh >> fb) & 1u ? 0u : 1u;
-#pragma unroll
-        for (int ks = 0; ks < 8; ks++) {
-            mma_f16(tmem + c.w2, d.a3m + 128u * ks, d.a1m + 128u * ks, id_dw, ks > 0 ? 1u : acc0);
-            mma_f16(tmem + c.xe2, d.a3m + 128u * ks, d.xe + 16u * ks, id_n8, ks > 0 ? 1u : acc0);
+            for (int ks = 0; ks < 4; ks++) mma_f16(Z, da + 2u * ks, db + 2u * ks, id_fwd, ks > 0);
+            mma_commit(doneZ);
         }
-        d.fresh &= ~(3u << fb);
-        mma_commit(doneW);
-    } else {
-        const uint32_t acc0 = (d.fresh >> (fb + 2)) & 1u ? 0u : 1u;
+    } else if (ST == 1) {
+        const uint32_t acc0 = (fresh >> (fb + 3)) & 1u ? 0u : 1u;
+        const uint64_t da = act_desc_mnmajor(A2, 0), db = narrow_desc_mnmajor(wb + L.dout[net], TC_ROWS, 0);
+        const uint32_t id = net == 0 ? idesc_f16(FMT, 64, L.n3a, 1, 1) : id_n8;
+        if (lead) {
 #pragma unroll
-        for (int ks = 0; ks < 8; ks++) mma_f16(tmem + c.xe1, d.a2m + 128u * ks, d.xe + 16u * ks, id_n8, ks > 0 ? 1u : acc0);
-        d.fresh &= ~(1u << (fb + 2));
-        mma_commit(doneW);
+            for (int ks = 0; ks < 8; ks++) mma_f16(tmem + c.w3, da + 128u * ks, db + 16u * ks, id, ks > 0 ? 1u : acc0);
+            mma_commit(doneW);
+        }
+        w.fresh &= ~(1u << (fb + 3));
+    } else if (ST == 2) {
+        const uint64_t dak = act_desc_kmajor(A2, 0), dam = act_desc_mnmajor(A2, 0);
+        const uint64_t dw = act_desc_mnmajor(W2, 0), dh = act_desc_mnmajor(A1, 0);
+        const uint64_t dx = narrow_desc_mnmajor(wb + L.xe[par], TC_ROWS, 0);
+        const uint32_t acc0 = (fresh >> fb) & 1u ? 0u : 1u;
+        if (lead) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) mma_f16(Z, dak + 2u * ks, dw + 128u * ks, id_dx, ks > 0);
+            mma_commit(doneZ);
+#pragma unroll
+            for (int ks = 0; ks < 8; ks++) {
+                mma_f16(tmem + c.w2, dam + 128u * ks, dh + 128u * ks, id_dw, ks > 0 ? 1u : acc0);
+                mma_f16(tmem + c.xe2, dam + 128u * ks, dx + 16u * ks, id_n8, ks > 0 ? 1u : acc0);
+            }
+            mma_commit(doneW);
+        }
+        w.fresh &= ~(3u << fb);
+    } else {
+        const uint64_t dam = act_desc_mnmajor(A2, 0), dx = narrow_desc_mnmajor(wb + L.xe[par], TC_ROWS, 0);
+        const uint32_t acc0 = (fresh >> (fb + 2)) & 1u ? 0u : 1u;
+        if (lead) {
+#pragma unroll
+            for (int ks = 0; ks < 8; ks++) mma_f16(tmem + c.xe1, dam + 128u * ks, dx + 16u * ks, id_n8, ks > 0 ? 1u : acc0);
+            mma_commit(doneW);
+        }
+        w.fresh &= ~(1u << (fb + 2));
     }
+    __syncwarp();
 }
 
 // ---- per-row pieces of a compute warpgroup --------------------------------------------------------------------
 // layer 1 for 8 consecutive hidden units j0..j0+7: h = tanh(sum_i xe[i] P1[j][i]); P1 row = {W1[j][0..O), b1[j], 0..}
-__device__ __forceinline__ void layer1_chunk(const float* P1, const float (&xe)[8], bool wide, int j0, float* h) {
+template <bool WIDE>
+__device__ __forceinline__ void layer1_chunk(const float* P1, const float (&xe)[8], int j0, float* h) {
 #pragma unroll
     for (int jj = 0; jj < 8; jj++) {
         const float4 w0 = *reinterpret_cast<const float4*>(P1 + (j0 + jj) * 8);
         float acc = xe[0] * w0.x;
         acc = fmaf(xe[1], w0.y, acc); acc = fmaf(xe[2], w0.z, acc); acc = fmaf(xe[3], w0.w, acc);
-        if (wide) {
+        if (WIDE) {
             const float4 w1 = *reinterpret_cast<const float4*>(P1 + (j0 + jj) * 8 + 4);
             acc = fmaf(xe[4], w1.x, acc); acc = fmaf(xe[5], w1.y, acc);
             acc = fmaf(xe[6], w1.z, acc); acc = fmaf(xe[7], w1.w, acc);
@@ -170,7 +202,7 @@ __device__ __forceinline__ void layer1_chunk(const float* P1, const float (&xe)[
     }
 }
 
-template <int FMT, int NWG>
+template <int FMT, int NWG, bool WIDE>
 __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -178,18 +210,17 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
     const TcLayout L = tc_layout(K, NWG);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const NetOff offs[2] = {actor_off(O, TC_H, K), critic_off(O, TC_H)};
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + L.bars);  // doneZ[NWG + g], doneW[2 NWG + g]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + L.bars);  // [(g * 2 + net) * 2 + {doneZ, doneW}]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + L.tmem_slot);
     const int ntiles = (a.mb_size + TC_ROWS - 1) / TC_ROWS;
     const int nthreads = NWG * 128;
+    long long* ts_buf = (blockIdx.x == 0 && tid == g_tc_ts_who) ? g_tc_ts : nullptr;
+    TC_TS(0);
 
     // ---------------- prologue: tensor memory, barriers, parameters -> shared memory -------------------------
     if (warp == 0) tmem_alloc(tmem_slot, 512);
     if (tid == 0) {
-        for (int g = 0; g < NWG; g++) {
-            mbar_init(bars + NWG + g, 1);
-            mbar_init(bars + 2 * NWG + g, 1);
-        }
+        for (int i = 0; i < NWG * 4; i++) mbar_init(bars + i, 1);   // [(g * 2 + net) * 2 + {doneZ, doneW}]
         mbar_init_fence();
     }
     {   // W2 of both nets as 16-bit activation-layout tiles: 1024 chunk tasks, all loads of a thread in flight together
@@ -252,41 +283,24 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    TC_TS(1);
 
-    RowSums rs;
+    RowSumsF rs;
     float gb3c = 0.0f;  // critic output-bias gradient partial of this thread
     {
         // ---------------- compute warpgroup ------------------------------------------------------------------
         const int g = warp >> 2, wt = tid & 127, w4 = warp & 3;
         uint8_t* wg = sm + L.wg0 + g * L.wg_stride;
-        uint8_t *A1 = wg + L.a1, *A2 = wg + L.a2, *A3 = wg + L.a3, *XE = wg + L.xe, *DO = wg + L.dout;
         float* x = reinterpret_cast<float*>(wg + L.lg) + wt * L.ldo;     // this row's logits / dL/dlogits
         float* b3acc = reinterpret_cast<float*>(wg + L.b3) + wt * L.ldo; // this thread's actor db3 partials
         for (int q = 0; q < K; q++) b3acc[q] = 0.0f;
-        uint64_t *doneZ = bars + NWG + g, *doneW = bars + 2 * NWG + g;
-        WgDescs D;
-        {
-            const uint32_t wb = smem_u32(wg);
-            D.a1k = act_desc_kmajor(wb + L.a1, 0); D.a1m = act_desc_mnmajor(wb + L.a1, 0);
-            D.a2m = act_desc_mnmajor(wb + L.a2, 0);
-            D.a3k = act_desc_kmajor(wb + L.a3, 0); D.a3m = act_desc_mnmajor(wb + L.a3, 0);
-            D.xe = narrow_desc_mnmajor(wb + L.xe, TC_ROWS, 0); D.dout = narrow_desc_mnmajor(wb + L.dout, TC_ROWS, 0);
-            for (int n = 0; n < 2; n++) {
-                D.w2k[n] = act_desc_kmajor(smem_u32(sm) + L.w2[n], 0);
-                D.w2m[n] = act_desc_mnmajor(smem_u32(sm) + L.w2[n], 0);
-                D.c[n] = tc_cols(NWG, g, n, L.n3a);
-            }
-            D.Z = tmem + (uint32_t)g * 64u;
-            D.id_w3[0] = idesc_f16(FMT, 64, L.n3a, 1, 1);
-            D.id_w3[1] = idesc_f16(FMT, 64, 8, 1, 1);
-            D.fresh = 0xFFu;
-        }
+        WgIssue D;
+        D.wb = smem_u32(wg); D.sb = smem_u32(sm); D.tmem = tmem; D.g = g; D.fresh = 0xFFu;
         const int barid = 1 + g;
-        uint32_t pz = 0, pw = 0;
-        bool pendingW = false;
-        const uint32_t zaddr = tmem_addr(tmem, (uint32_t)w4 * 32u, (uint32_t)g * 64u);
+        uint64_t* wbars = bars + g * 4;          // [net * 2 + {doneZ, doneW}]
+        uint32_t pz[2] = {0u, 0u}, pw[2] = {0u, 0u};
+        bool pendingW = false;                   // G4 of the previous tile not yet waited for (both nets)
         const bool masked = a.mask != nullptr;
-        const bool wide = O + 1 > 4;
         float meanf = 0.0f, stdf = 1.0f;
         if (a.hp.norm_adv) { meanf = a.adv_stats[0]; stdf = a.adv_stats[1]; }
         const int nwg_total = gridDim.x * NWG;
@@ -297,6 +311,7 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
             int64_t r;
             float o[4];      // obs (O <= 4: prefetched; wider observations are loaded at use)
             float old_logp, adv, ret, old_val;
+            int act0;        // action of head 0 (single-head fast path)
             bool on;
         };
         auto gather = [&](int tile) {
@@ -306,6 +321,7 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
             in.r = 0;
             in.o[0] = in.o[1] = in.o[2] = in.o[3] = 0.0f;
             in.old_logp = in.adv = in.ret = in.old_val = 0.0f;
+            in.act0 = 0;
             if (in.on) {
                 const int64_t r = a.perm ? (int64_t)__ldg(a.perm + a.mb_start + rloc) : a.mb_start + rloc;
                 in.r = r;
@@ -318,6 +334,7 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
                         if (i < O) in.o[i] = __ldg(a.obs + r * O + i);
                 }
                 in.old_logp = __ldg(a.old_logprob + r);
+                in.act0 = __ldg(a.actions + r * heads);
                 in.adv = __ldg(a.adv + r);
                 in.ret = __ldg(a.ret + r);
                 if (a.hp.clip_vloss) in.old_val = __ldg(a.old_val + r);
@@ -325,6 +342,7 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
             return in;
         };
         RowIn nxt = gather(blockIdx.x * NWG + g);
+        int tiles_done = 0;
         for (int tile = blockIdx.x * NWG + g; tile < ntiles; tile += nwg_total) {
             const RowIn cur = nxt;
             nxt = gather(tile + nwg_total);
@@ -345,30 +363,48 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
             for (int i = 0; i < 8; i++)
                 if (i == O) xe[i] = 1.0f;
 
+            const int tsb = 8 + tiles_done * 40;
+            TC_TS(tsb);
+            const int par = tiles_done & 1;      // XE is double-buffered: G3b / G4 of the previous tile may still read it
+            tiles_done++;
+            store8<FMT>(wg + L.xe[par] + wt * 16, xe);
+            float gvc = 0.0f;                     // critic dL/dvalue of this row (lives from P2 to P3)
+
+            // ---- P1: layer 1 -> A1[net]; G1
+#pragma unroll 1
             for (int net = 0; net < 2; net++) {
-                const int k3 = net == 0 ? K : 1;
                 const float* P1 = reinterpret_cast<const float*>(sm + L.p1[net]);
-                const float* B2 = reinterpret_cast<const float*>(sm + L.b2[net]);
-                const float* W3 = reinterpret_cast<const float*>(sm + L.w3[net]);
-                const float* B3 = reinterpret_cast<const float*>(sm + L.b3p[net]);
-                if (pendingW) {  // G4 of the previous pass: every operand buffer of this warpgroup is free again
-                    mbar_wait(doneW, pw); pw ^= 1u; pendingW = false;
-                }
-                if (net == 0) store8<FMT>(XE + wt * 16, xe);
-                // ---- S1: layer 1 -> A1
+                uint8_t* A1 = wg + L.a1[net];
 #pragma unroll
                 for (int c = 0; c < 8; c++) {
                     float h[8];
-                    layer1_chunk(P1, xe, wide, c * 8, h);
+                    layer1_chunk<WIDE>(P1, xe, c * 8, h);
                     store8<FMT>(A1 + act_chunk_off(wt, c), h);
                 }
                 fence_async_smem();
+                TC_TS(tsb + 1 + net * 3);
                 bar_sync(barid, 128);
-                if (wt == 0) issue_stage<FMT, 0>(D, net, tmem, doneZ, doneW);
-                mbar_wait(doneZ, pz); pz ^= 1u;
+                TC_TS(tsb + 2 + net * 3);
+                if (w4 == 0) issue_stage<FMT, NWG, 0>(D, L, net, par, wbars + net * 2, wbars + net * 2 + 1);
+                TC_TS(tsb + 3 + net * 3);
+            }
+            // ---- P2: h2 = tanh(Z + b2) -> A2[net]; output layer; loss; dOut -> DO[net]; G5
+#pragma unroll 1
+            for (int net = 0; net < 2; net++) {
+                const int k3 = net == 0 ? K : 1;
+                const float* B2 = reinterpret_cast<const float*>(sm + L.b2[net]);
+                const float* W3 = reinterpret_cast<const float*>(sm + L.w3[net]);
+                const float* B3 = reinterpret_cast<const float*>(sm + L.b3p[net]);
+                uint8_t *A2 = wg + L.a2[net], *DO = wg + L.dout[net];
+                uint64_t *doneZ = wbars + net * 2, *doneW = doneZ + 1;
+                if (pendingW) {  // G4 of the previous tile has read A2[net]
+                    mbar_wait(doneW, pw[net]); pw[net] ^= 1u;
+                }
+                mbar_wait(doneZ, pz[net]); pz[net] ^= 1u;
                 tc_fence_after();
-                // ---- S2: h2 = tanh(Z + b2) -> A2; output layer; loss; dOut -> DO
+                TC_TS(tsb + 7 + net * 4);
                 float h2[64];
+                const uint32_t zaddr = tmem_addr(tmem, (uint32_t)w4 * 32u, (uint32_t)(g * 2 + net) * 64u);
 #pragma unroll
                 for (int c = 0; c < 4; c++) tmem_ld16(zaddr + c * 16, h2 + c * 16);
                 tmem_ld_wait();
@@ -382,20 +418,25 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
                 for (int c = 0; c < 8; c++) store8<FMT>(A2 + act_chunk_off(wt, c), h2 + c * 8);
                 float gv = 0.0f;
                 for (int q = 0; q < k3; q++) {
-                    float acc = B3[q];
+                    float a0 = B3[q], a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;   // four chains instead of one 64-deep one
 #pragma unroll
                     for (int c = 0; c < 16; c++) {
                         const float4 w = *reinterpret_cast<const float4*>(W3 + q * TC_H + c * 4);
-                        acc = fmaf(h2[c * 4 + 0], w.x, acc); acc = fmaf(h2[c * 4 + 1], w.y, acc);
-                        acc = fmaf(h2[c * 4 + 2], w.z, acc); acc = fmaf(h2[c * 4 + 3], w.w, acc);
+                        a0 = fmaf(h2[c * 4 + 0], w.x, a0); a1 = fmaf(h2[c * 4 + 1], w.y, a1);
+                        a2 = fmaf(h2[c * 4 + 2], w.z, a2); a3 = fmaf(h2[c * 4 + 3], w.w, a3);
                     }
-                    if (net == 0) x[q] = acc; else gv = acc;
+                    gv = (a0 + a1) + (a2 + a3);
+                    if (net == 0) x[q] = gv;
                 }
                 if (net == 0) {
                     if (on) {
-                        const uint64_t mbits = masked ? pack_mask(a.mask + r * K, K) : ~0ull;
-                        actor_row_loss(x, a.d, masked, mbits, a.actions + r * heads, cur.old_logp, cur.adv, a.hp, meanf, stdf,
-                                       1.0f, rs);
+                        if (heads == 1 && !masked) {
+                            actor_row_loss_fast1(x, K, cur.act0, cur.old_logp, cur.adv, a.hp, meanf, stdf, rs);
+                        } else {
+                            const uint64_t mbits = masked ? pack_mask(a.mask + r * K, K) : ~0ull;
+                            actor_row_loss(x, a.d, masked, mbits, a.actions + r * heads, cur.old_logp, cur.adv, a.hp, meanf,
+                                           stdf, 1.0f, rs);
+                        }
                         for (int q = 0; q < K; q++) b3acc[q] += x[q];
                     } else {
                         for (int q = 0; q < K; q++) x[q] = 0.0f;
@@ -407,21 +448,32 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
                         store8<FMT>(DO + c * (TC_ROWS * 16) + wt * 16, v);
                     }
                 } else {
-                    gv = on ? critic_row_loss(gv, cur.ret, cur.old_val, a.hp, 1.0f, rs) : 0.0f;
-                    gb3c += gv;
-                    float v[8] = {gv, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                    gvc = on ? critic_row_loss(gv, cur.ret, cur.old_val, a.hp, 1.0f, rs) : 0.0f;
+                    gb3c += gvc;
+                    float v[8] = {gvc, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                     store8<FMT>(DO + wt * 16, v);
                 }
                 tc_fence_before();
                 fence_async_smem();
+                TC_TS(tsb + 8 + net * 4);
                 bar_sync(barid, 128);
-                if (wt == 0) issue_stage<FMT, 1>(D, net, tmem, doneZ, doneW);
-                // ---- S3: dZ2 = (dOut W3) * (1 - h2^2) -> A3
+                TC_TS(tsb + 9 + net * 4);
+                if (w4 == 0) issue_stage<FMT, NWG, 1>(D, L, net, par, doneZ, doneW);
+                TC_TS(tsb + 10 + net * 4);
+            }
+            pendingW = false;
+            // ---- P3: dZ2 = (dOut W3) * (1 - h2^2) -> A2[net] (over h2, once G5 has read it); G2, G3
+#pragma unroll 1
+            for (int net = 0; net < 2; net++) {
+                const int k3 = net == 0 ? K : 1;
+                const float* W3 = reinterpret_cast<const float*>(sm + L.w3[net]);
+                uint8_t* A2 = wg + L.a2[net];
+                uint64_t *doneZ = wbars + net * 2, *doneW = doneZ + 1;
                 float d[64];
 #pragma unroll
                 for (int k = 0; k < 64; k++) d[k] = 0.0f;
                 for (int q = 0; q < k3; q++) {
-                    const float dq = net == 0 ? x[q] : gv;
+                    const float dq = net == 0 ? x[q] : gvc;
 #pragma unroll
                     for (int c = 0; c < 16; c++) {
                         const float4 w = *reinterpret_cast<const float4*>(W3 + q * TC_H + c * 4);
@@ -430,16 +482,34 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
                     }
                 }
 #pragma unroll
-                for (int k = 0; k < 64; k++) d[k] *= fmaf(-h2[k], h2[k], 1.0f);
-                mbar_wait(doneW, pw); pw ^= 1u;  // G5 has read A2 / DO
+                for (int c = 0; c < 8; c++) {   // h2 comes back from its 16-bit copy (this thread wrote it in P2)
+                    float h2[8];
+                    load8<FMT>(A2 + act_chunk_off(wt, c), h2);
 #pragma unroll
-                for (int c = 0; c < 8; c++) store8<FMT>(A3 + act_chunk_off(wt, c), d + c * 8);
+                    for (int i = 0; i < 8; i++) d[c * 8 + i] *= fmaf(-h2[i], h2[i], 1.0f);
+                }
+                TC_TS(tsb + 15 + net * 4);
+                mbar_wait(doneW, pw[net]); pw[net] ^= 1u;  // G5 has read A2 / DO
+                TC_TS(tsb + 16 + net * 4);
+#pragma unroll
+                for (int c = 0; c < 8; c++) store8<FMT>(A2 + act_chunk_off(wt, c), d + c * 8);
                 fence_async_smem();
                 bar_sync(barid, 128);
-                if (wt == 0) issue_stage<FMT, 2>(D, net, tmem, doneZ, doneW);
-                mbar_wait(doneZ, pz); pz ^= 1u;
+                TC_TS(tsb + 17 + net * 4);
+                if (w4 == 0) issue_stage<FMT, NWG, 2>(D, L, net, par, doneZ, doneW);
+                TC_TS(tsb + 18 + net * 4);
+            }
+            // ---- P4: dZ1 = Z * (1 - h1^2) -> A2[net] (once G2 / G3 have read dZ2); G4
+#pragma unroll 1
+            for (int net = 0; net < 2; net++) {
+                uint8_t *A1 = wg + L.a1[net], *A2 = wg + L.a2[net];
+                uint64_t *doneZ = wbars + net * 2, *doneW = doneZ + 1;
+                TC_TS(tsb + 23 + net * 6);
+                mbar_wait(doneZ, pz[net]); pz[net] ^= 1u;
                 tc_fence_after();
-                // ---- S4: dZ1 = Z * (1 - h1^2) -> A2 (h2's buffer; G5 is done with it)
+                TC_TS(tsb + 24 + net * 6);
+                float d[64];
+                const uint32_t zaddr = tmem_addr(tmem, (uint32_t)w4 * 32u, (uint32_t)(g * 2 + net) * 64u);
 #pragma unroll
                 for (int c = 0; c < 4; c++) tmem_ld16(zaddr + c * 16, d + c * 16);
                 tmem_ld_wait();
@@ -449,105 +519,111 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
                     load8<FMT>(A1 + act_chunk_off(wt, c), h1);
 #pragma unroll
                     for (int i = 0; i < 8; i++) d[c * 8 + i] *= fmaf(-h1[i], h1[i], 1.0f);
-                    store8<FMT>(A2 + act_chunk_off(wt, c), d + c * 8);
                 }
-                mbar_wait(doneW, pw); pw ^= 1u;  // G3 has read A1 / A3 (keeps doneW in lock-step)
+                TC_TS(tsb + 25 + net * 6);
+                mbar_wait(doneW, pw[net]); pw[net] ^= 1u;  // G3 has read A1 / A2
+                TC_TS(tsb + 26 + net * 6);
+#pragma unroll
+                for (int c = 0; c < 8; c++) store8<FMT>(A2 + act_chunk_off(wt, c), d + c * 8);
                 tc_fence_before();
                 fence_async_smem();
                 bar_sync(barid, 128);
-                if (wt == 0) issue_stage<FMT, 3>(D, net, tmem, doneZ, doneW);
-                pendingW = true;
+                TC_TS(tsb + 27 + net * 6);
+                if (w4 == 0) issue_stage<FMT, NWG, 3>(D, L, net, par, doneZ, doneW);
+                TC_TS(tsb + 28 + net * 6);
             }
+            pendingW = true;
         }
-        if (pendingW) { mbar_wait(doneW, pw); pw ^= 1u; }
+        if (pendingW) {
+            mbar_wait(wbars + 1, pw[0]);
+            mbar_wait(wbars + 3, pw[1]);
+        }
     }
 
     // ---------------- drain: tensor-memory accumulators -> this CTA's slab (x 1/n), diagnostics ----------------
+    TC_TS(2);
     tc_fence_before();
     __syncthreads();
+    TC_TS(3);
     tc_fence_after();
     const int P = num_params(O, TC_H, K);
     float* slab = a.slabs + (size_t)blockIdx.x * slab_stride(P);
     const float sc = a.inv_n;
     if (warp < 4) {
-        // M = 64 accumulators: row m sits in lane (m % 16) + 32 (m / 16)  =>  lanes 0..15 of warp w hold rows 16 w + lane
-        const int n = 16 * warp + lane;
-        const bool has = lane < 16;
+        // M = 64 accumulators: row m sits in lane (m % 16) + 32 (m / 16); the actor's use lanes 0..15 of each
+        // subpartition and the critic's lanes 16..31, so one load serves both nets: lane l of warp w holds row
+        // 16 w + (l & 15) of net (l >> 4).
+        const int n = 16 * warp + (lane & 15);
+        const int net = lane >> 4;
+        const NetOff& of = offs[net];
+        const int k3 = net == 0 ? K : 1;
         const uint32_t la = tmem_addr(tmem, (uint32_t)warp * 32u, 0);
-        // warpgroups that owned no tile never wrote their accumulators: skip them (same test as the issuer's)
+        // warpgroups that owned no tile never wrote their accumulators: skip them
         int ng = 0;
         for (int g = 0; g < NWG; g++)
             if (blockIdx.x * NWG + g < ntiles) ng = g + 1;
-        for (int net = 0; net < 2; net++) {
-            const NetOff& of = offs[net];
-            const int k3 = net == 0 ? K : 1;
-            float v[64], w[64];
+        float v[64], w[64];
+#pragma unroll
+        for (int g = 0; g < NWG; g++) {
+            if (g >= ng) break;
+            const uint32_t base = la + tc_cols(NWG, g, 0, L.n3a).w2;
+#pragma unroll
+            for (int cc = 0; cc < 4; cc++) tmem_ld16(base + cc * 16, (g == 0 ? v : w) + cc * 16);
+            tmem_ld_wait();
+            if (g > 0)
+#pragma unroll
+                for (int k = 0; k < 64; k++) v[k] += w[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 64; k++) slab[of.W2 + n * TC_H + k] = v[k] * sc;
+        float e[8], f[8];
+#pragma unroll
+        for (int g = 0; g < NWG; g++) {
+            if (g >= ng) break;
+            tmem_ld8(la + tc_cols(NWG, g, 0, L.n3a).xe2, g == 0 ? e : f);
+            tmem_ld_wait();
+            if (g > 0)
+#pragma unroll
+                for (int i = 0; i < 8; i++) e[i] += f[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            if (i == O) slab[of.b2 + n] = e[i] * sc;
+#pragma unroll
+        for (int g = 0; g < NWG; g++) {
+            if (g >= ng) break;
+            tmem_ld8(la + tc_cols(NWG, g, 0, L.n3a).xe1, g == 0 ? e : f);
+            tmem_ld_wait();
+            if (g > 0)
+#pragma unroll
+                for (int i = 0; i < 8; i++) e[i] += f[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            if (i < O) slab[of.W1 + n * O + i] = e[i] * sc;
+            if (i == O) slab[of.b1 + n] = e[i] * sc;
+        }
+        for (int cc = 0; cc < L.n3a / 8; cc++) {   // critic lanes only own chunk 0 (the actor's other chunks map to junk there)
 #pragma unroll
             for (int g = 0; g < NWG; g++) {
                 if (g >= ng) break;
-                const TcCols c = tc_cols(NWG, g, net, L.n3a);
-#pragma unroll
-                for (int cc = 0; cc < 4; cc++) tmem_ld16(la + c.w2 + cc * 16, (g == 0 ? v : w) + cc * 16);
-                tmem_ld_wait();
-                if (g > 0)
-#pragma unroll
-                    for (int k = 0; k < 64; k++) v[k] += w[k];
-            }
-            if (has)
-#pragma unroll
-                for (int k = 0; k < 64; k++) slab[of.W2 + n * TC_H + k] = v[k] * sc;
-            float e[8], f[8];
-#pragma unroll
-            for (int g = 0; g < NWG; g++) {
-                if (g >= ng) break;
-                tmem_ld8(la + tc_cols(NWG, g, net, L.n3a).xe2, g == 0 ? e : f);
+                tmem_ld8(la + tc_cols(NWG, g, 0, L.n3a).w3 + cc * 8, g == 0 ? e : f);
                 tmem_ld_wait();
                 if (g > 0)
 #pragma unroll
                     for (int i = 0; i < 8; i++) e[i] += f[i];
             }
-            if (has)
 #pragma unroll
-                for (int i = 0; i < 8; i++)
-                    if (i == O) slab[of.b2 + n] = e[i] * sc;
-#pragma unroll
-            for (int g = 0; g < NWG; g++) {
-                if (g >= ng) break;
-                tmem_ld8(la + tc_cols(NWG, g, net, L.n3a).xe1, g == 0 ? e : f);
-                tmem_ld_wait();
-                if (g > 0)
-#pragma unroll
-                    for (int i = 0; i < 8; i++) e[i] += f[i];
-            }
-            if (has)
-#pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    if (i < O) slab[of.W1 + n * O + i] = e[i] * sc;
-                    if (i == O) slab[of.b1 + n] = e[i] * sc;
-                }
-            for (int cc = 0; cc < ((k3 + 7) >> 3); cc++) {
-#pragma unroll
-                for (int g = 0; g < NWG; g++) {
-                    if (g >= ng) break;
-                    tmem_ld8(la + tc_cols(NWG, g, net, L.n3a).w3 + cc * 8, g == 0 ? e : f);
-                    tmem_ld_wait();
-                    if (g > 0)
-#pragma unroll
-                        for (int i = 0; i < 8; i++) e[i] += f[i];
-                }
-                if (has)
-#pragma unroll
-                    for (int i = 0; i < 8; i++)
-                        if (cc * 8 + i < k3) slab[of.W3 + (cc * 8 + i) * TC_H + n] = e[i] * sc;
-            }
+            for (int i = 0; i < 8; i++)
+                if (cc * 8 + i < k3) slab[of.W3 + (cc * 8 + i) * TC_H + n] = e[i] * sc;
         }
     }
     constexpr int NT = NWG * 128;
     double* red = reinterpret_cast<double*>(sm + L.wg0);                    // [5][NT]   (A1/A2 of warpgroup 0)
     float* gbc = reinterpret_cast<float*>(sm + L.wg0 + 5 * NT * 8);         // [NT]
     {
-        red[0 * NT + tid] = rs.pg; red[1 * NT + tid] = rs.v; red[2 * NT + tid] = rs.ent;
-        red[3 * NT + tid] = rs.kl; red[4 * NT + tid] = rs.clip;
+        red[0 * NT + tid] = (double)rs.pg; red[1 * NT + tid] = (double)rs.v; red[2 * NT + tid] = (double)rs.ent;
+        red[3 * NT + tid] = (double)rs.kl; red[4 * NT + tid] = (double)rs.clip;
         gbc[tid] = gb3c;
     }
     __syncthreads();
@@ -578,17 +654,19 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
     }
     tc_fence_before();
     __syncthreads();
+    TC_TS(4);
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
-template <int FMT, int NWG>
+template <int FMT, int NWG, bool WIDE>
 static int launch_tc(const UpdArgs& a, int* grid_out, cudaStream_t st) {
     const TcLayout L = tc_layout(a.d.K, NWG);
     const size_t smem = (size_t)L.end + 1024;
     PPO_REQUIRE(smem <= 227 * 1024, "update_tc: needs %zu B of shared memory", smem);
     static bool attr_done = false;
     if (!attr_done) {
-        PPO_CUDA(cudaFuncSetAttribute(update_tc_kernel<FMT, NWG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        PPO_CUDA(cudaFuncSetAttribute(update_tc_kernel<FMT, NWG, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      227 * 1024));
         attr_done = true;
     }
     const int ntiles = (a.mb_size + TC_ROWS - 1) / TC_ROWS;
@@ -596,16 +674,27 @@ static int launch_tc(const UpdArgs& a, int* grid_out, cudaStream_t st) {
     int grid = (ntiles + NWG - 1) / NWG;
     if (grid > sms) grid = sms;
     if (grid > UPD_MAX_GRID) grid = UPD_MAX_GRID;
-    update_tc_kernel<FMT, NWG><<<grid, NWG * 128, smem, st>>>(a);
+    update_tc_kernel<FMT, NWG, WIDE><<<grid, NWG * 128, smem, st>>>(a);
     PPO_LAUNCH_CHECK();
     *grid_out = grid;
     return PPO_OK;
 }
 
+}  // namespace ppo
+// d_ts: device buffer of 256 int64 (or NULL to switch off): later update_tc launches stamp the SM clock of CTA 0,
+// thread `who` at fixed points (slot map in tools/tc_timeline.py)
+extern "C" int ppo_debug_tc_timeline(long long* d_ts, int who) {
+    PPO_CUDA(cudaMemcpyToSymbol(ppo::g_tc_ts, &d_ts, sizeof(d_ts)));
+    PPO_CUDA(cudaMemcpyToSymbol(ppo::g_tc_ts_who, &who, sizeof(who)));
+    return PPO_OK;
+}
+namespace ppo {
 int launch_update_tc(const UpdArgs& a, int fmt, int* grid_out, cudaStream_t st) {
     if (a.d.H != TC_H || a.d.O + 1 > 8 || a.d.K > TC_MAX_K) return PPO_ERR_UNSUPPORTED;
-    if (fmt == FMT_BF16) return launch_tc<FMT_BF16, 2>(a, grid_out, st);
-    return launch_tc<FMT_F16, 2>(a, grid_out, st);
+    if ((size_t)tc_layout(a.d.K, 2).end + 1024 > 227 * 1024) return PPO_ERR_UNSUPPORTED;
+    const bool wide = a.d.O + 1 > 4;
+    if (fmt == FMT_BF16) return wide ? launch_tc<FMT_BF16, 2, true>(a, grid_out, st) : launch_tc<FMT_BF16, 2, false>(a, grid_out, st);
+    return wide ? launch_tc<FMT_F16, 2, true>(a, grid_out, st) : launch_tc<FMT_F16, 2, false>(a, grid_out, st);
 }
 
 }  // namespace ppo
