@@ -364,17 +364,20 @@ def run_b200(args, wl_name):
     upd_ms_per = upd_ms / max(1, upd_cnt)
     achieved_tf = flops_per_launch / (upd_ms_per / 1000.0) / 1e12
     phase_total = sum(v[0] for v in phases.values())
-    roofline = {"bound": "tensor", "kernel": "update_kernel (fused fwd + PPO loss + bwd, fp32 FMA path)",
+    mode = P.ops.get_math_mode()
+    mode_name = {0: "fp32 FMA path (update_kernel)", 1: "bf16 tcgen05 path (update_tc_kernel)",
+                 2: "fp16 tcgen05 path (update_tc_kernel)"}[mode]
+    roofline = {"bound": "tensor", "kernel": "fused fwd + PPO loss + bwd, " + mode_name,
                 "achieved": achieved_tf, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
                 "frac": achieved_tf / pk["bf16_sustained"], "traffic": None, "peak_source": pk["source"] +
-                " (bf16 cuBLAS sustained; the kernel computes in fp32 on the FMA pipe)",
+                " (bf16 cuBLAS sustained)",
                 "flops_per_launch": flops_per_launch, "ms_per_launch": upd_ms_per,
                 "share_of_step": upd_ms / phase_total if phase_total else None}
     launches = 1 + 1 + 1 + wl["E"] * (2 + wl["MB"] * 3) + 1     # scalars, rollout, gae, per epoch, ev
 
     line = {"metric": "env_steps_per_sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
+            "dtype": {0: "f32", 1: "bf16", 2: "f16"}[mode], "data": "synthetic",
             "config": {"workload": wl_name, "env": "CartPole" if wl["env"] == 0 else "MountainCar",
                        "envs_per_gpu": wl["N"], "rollout_steps": wl["T"], "hidden": wl["H"], "update_epochs": wl["E"],
                        "minibatches": wl["MB"], "global_batch": batch * world, "parallelism": f"dp{world}",
