@@ -40,10 +40,23 @@ __global__ void __launch_bounds__(CAT_ROWS) categorical_kernel(const CatArgs a) 
     {
         const float* src = a.logits + r0 * K;
         const int total = rows * K;
-        for (int e = t; e < total; e += CAT_ROWS) xs[(e / K) * ld + (e % K)] = __ldg(src + e);
+        // (row, col) of element e tracked incrementally: no per-element division
+        const int qs = CAT_ROWS / K, rs = CAT_ROWS % K;
+        int row = t / K, col = t % K;
+        for (int e = t; e < total; e += CAT_ROWS) {
+            xs[row * ld + col] = __ldg(src + e);
+            row += qs; col += rs;
+            if (col >= K) { col -= K; row++; }
+        }
         if (a.mask) {
-            const uint8_t* msrc = a.mask + r0 * K;
-            for (int e = t; e < total; e += CAT_ROWS) ms[e] = __ldg(msrc + e);
+            const uint8_t* msrc = a.mask + r0 * K;   // tile base is 128*K bytes in: word-aligned when the buffer is
+            if (rows == CAT_ROWS && (reinterpret_cast<uintptr_t>(msrc) & 3) == 0) {
+                const uint32_t* m4 = reinterpret_cast<const uint32_t*>(msrc);
+                uint32_t* d4 = reinterpret_cast<uint32_t*>(ms);
+                for (int e = t; e < total / 4; e += CAT_ROWS) d4[e] = __ldg(m4 + e);
+            } else {
+                for (int e = t; e < total; e += CAT_ROWS) ms[e] = __ldg(msrc + e);
+            }
         }
         const int th = rows * a.heads;
         if (a.actions_in)
@@ -83,7 +96,13 @@ __global__ void __launch_bounds__(CAT_ROWS) categorical_kernel(const CatArgs a) 
     }
     if (a.probs_out) {
         const int total = rows * K;
-        for (int e = t; e < total; e += CAT_ROWS) a.probs_out[r0 * K + e] = xs[(e / K) * ld + (e % K)];
+        const int qs = CAT_ROWS / K, rs = CAT_ROWS % K;
+        int row = t / K, col = t % K;
+        for (int e = t; e < total; e += CAT_ROWS) {
+            a.probs_out[r0 * K + e] = xs[row * ld + col];
+            row += qs; col += rs;
+            if (col >= K) { col -= K; row++; }
+        }
     }
 }
 
