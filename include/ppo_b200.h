@@ -308,6 +308,12 @@ int ppo_trainer_set_comm(ppo_trainer* t, ppo_comm* comm);
 int ppo_debug_umma_probe(int mode, int fmt, const float* A, const float* B, float* D, ppo_stream_t stream);
 /* Same GEMM issued `reps` times back to back by one thread; d_cycles[0] (device int64) = SM clocks from the first issue
  * to the completion of the last (how fast the tensor pipe retires each operand layout). */
+/* Rollout kernel choice for hidden = 64: 1 (default) = register-resident-weights kernel, 0 = the generic tiled kernel
+ * (what every other hidden width uses).  For A/B tests and benchmarks; no reference counterpart. */
+int ppo_debug_rollout_impl(int impl);
+/* d_ts = device buffer of 8 int64 (NULL switches it off): CTA 0 / thread 0 of the hidden = 64 rollout kernel stamps the
+ * SM clock at the six phase edges of rollout step 2 (tools/rollout_bench.py prints the deltas). */
+int ppo_debug_rollout_timeline(long long* d_ts);
 /* In-kernel timeline of the tensor-core update kernel: d_ts = device buffer of 256 int64 (NULL switches it off);
  * later launches stamp the SM clock of CTA 0, thread `who` at fixed points (tools/tc_timeline.py prints them). */
 int ppo_debug_tc_timeline(long long* d_ts, int who);

@@ -441,7 +441,11 @@ def test_permutation_is_bijection(P, batch):
 # ---------------------------------------------------------------------------------------------- rollout
 @pytest.mark.parametrize("kind,O,nvec,masked,H,n,T", [(0, 4, [2], False, 64, 100, 24), (0, 4, [1], False, 64, 8, 32),
                                                       (1, 2, [3], True, 64, 77, 20), (1, 2, [3], False, 256, 40, 6),
-                                                      (0, 4, [2], False, 128, 4096, 8)])
+                                                      (0, 4, [2], False, 128, 4096, 8),
+                                                      # hidden = 64 register-resident kernel: 32-env tiles (n > 32 SMs),
+                                                      # ragged last tile, multi-head
+                                                      (0, 4, [2], False, 64, 4999, 6),
+                                                      (1, 2, [3, 2], False, 64, 45, 12)])
 def test_fused_rollout_vs_oracle(P, orc, kind, O, nvec, masked, H, n, T):
     """Every step of the fused rollout is checked from the GPU's own previous observation (single-step
     comparisons, so CartPole's chaos cannot amplify ulp differences): forward -> sample on the same Philox
