@@ -154,6 +154,12 @@ __device__ __forceinline__ uint64_t narrow_desc_mnmajor(uint32_t base, int R, in
     return smem_desc(base + (uint32_t)ks * 256u, 128, (uint32_t)(R * 16), LAYOUT_NONE);
 }
 
+// narrow tile viewed K-major [MN = rows][K = 16], no swizzle: K chunk 0 at `base` (rows 16 B apart, 8-row core matrices
+// 128 B apart), K chunk 1 `chunk1_off` bytes further on (a second chunk of the same shape)
+__device__ __forceinline__ uint64_t narrow_desc_kmajor(uint32_t base, uint32_t chunk1_off) {
+    return smem_desc(base, chunk1_off, 128, LAYOUT_NONE);
+}
+
 // two fp32 -> one packed 16-bit pair (lo = first element)
 template <int FMT>
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {

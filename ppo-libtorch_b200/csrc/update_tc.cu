@@ -39,6 +39,7 @@ struct TcLayout {   // byte offsets into the 1024-aligned dynamic shared memory
     int w2[2];      // 16-bit W2 of actor (0) and critic (1), 64 rows x 128 B each
     int wg0, wg_stride;                  // per-warpgroup block
     int a1[2], a2[2], xe[2], dout[2], lg, b3;   // offsets inside a warpgroup block ([net], XE: [tile parity])
+    int p1h[2];                          // 16-bit P1 = {W1|b1|0} as K chunks {hi, hi, lo, 0} [4][64 units][8]: B of the layer-1 MMAs
     int p1[2], b2[2], w3[2], b3p[2];     // fp32 small parameters per net
     int bars, tmem_slot, end;
     int ldo, n3a;                        // logits row stride (floats), padded actor logit count
@@ -50,8 +51,8 @@ __host__ __device__ inline TcLayout tc_layout(int K, int nwg) {
     L.w2[0] = 0;
     L.w2[1] = 8192;
     L.a1[0] = 0; L.a1[1] = ACT_BYTES; L.a2[0] = 2 * ACT_BYTES; L.a2[1] = 3 * ACT_BYTES;
-    L.xe[0] = 4 * ACT_BYTES; L.xe[1] = L.xe[0] + TC_ROWS * 16;
-    L.dout[0] = L.xe[1] + TC_ROWS * 16;
+    L.xe[0] = 4 * ACT_BYTES; L.xe[1] = L.xe[0] + 2 * TC_ROWS * 16;   // per parity: 16-bit x (hi), then its residual (lo)
+    L.dout[0] = L.xe[1] + 2 * TC_ROWS * 16;
     L.dout[1] = L.dout[0] + (L.n3a / 8) * TC_ROWS * 16;
     L.lg = L.dout[1] + TC_ROWS * 16;
     L.b3 = L.lg + ((TC_ROWS * L.ldo * 4 + 15) & ~15);
@@ -65,6 +66,8 @@ __host__ __device__ inline TcLayout tc_layout(int K, int nwg) {
         L.w3[n] = o; o += k3 * TC_H * 4;
         L.b3p[n] = o; o += ((k3 + 3) & ~3) * 4;
     }
+    o = (o + 127) & ~127;
+    for (int n = 0; n < 2; n++) { L.p1h[n] = o; o += 4 * TC_H * 16; }
     L.bars = o; o += 4 * 4 * 8;
     L.tmem_slot = o; o += 16;
     L.end = o;
@@ -119,9 +122,12 @@ struct WgIssue {
     int g;
     uint32_t fresh;           // bit (net * 4 + accumulator): the next MMA into it must overwrite
 };
+// ST 0..3 = G1, G5, G2+G3, G4 (see the header); ST 4 = G0 alone: Z[net] = XE[par] P1h^T (layer-1 pre-activations, K = 16:
+// the 8 real inputs {obs, 1, 0..} + a zero chunk).  g0_next (ST 3 only): also issue G0 of the NEXT tile (XE[par ^ 1])
+// in front of G4 - Z[net] has just been read by P4 and is free.
 template <int FMT, int NWG, int ST>
 __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int net_, int par_, uint64_t* doneZ,
-                                            uint64_t* doneW) {
+                                            uint64_t* doneW, bool g0_next = false) {
     constexpr uint32_t id_fwd = idesc_f16(FMT, 128, 64, 0, 0);   // Z = A1 W2^T
     constexpr uint32_t id_dx = idesc_f16(FMT, 128, 64, 0, 1);    // Z = A2 W2
     constexpr uint32_t id_dw = idesc_f16(FMT, 64, 64, 1, 1);     // dW2 += A2^T A1
@@ -171,10 +177,28 @@ __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int n
             mma_commit(doneW);
         }
         w.fresh &= ~(3u << fb);
+    } else if (ST == 4) {
+        const uint64_t da = narrow_desc_kmajor(wb + L.xe[par], TC_ROWS * 16);          // {x.hi, x.lo}
+        const uint64_t db = narrow_desc_kmajor(sb + L.p1h[net], TC_H * 16);             // {P.hi, P.hi}
+        const uint64_t db2 = narrow_desc_kmajor(sb + L.p1h[net] + 2 * TC_H * 16, TC_H * 16);   // {P.lo, 0}
+        if (lead) {
+            mma_f16(Z, da, db, id_fwd, 0u);
+            mma_f16(Z, da, db2, id_fwd, 1u);
+            mma_commit(doneZ);
+        }
     } else {
         const uint64_t dam = act_desc_mnmajor(A2, 0), dx = narrow_desc_mnmajor(wb + L.xe[par], TC_ROWS, 0);
         const uint32_t acc0 = (fresh >> (fb + 2)) & 1u ? 0u : 1u;
+        const uint64_t da0 = narrow_desc_kmajor(wb + L.xe[par ^ 1], TC_ROWS * 16);
+        const uint64_t db0 = narrow_desc_kmajor(sb + L.p1h[net], TC_H * 16);
+        const uint64_t db1 = narrow_desc_kmajor(sb + L.p1h[net] + 2 * TC_H * 16, TC_H * 16);
+        const bool g0 = __shfl_sync(0xffffffffu, (int)g0_next, 0) != 0;
         if (lead) {
+            if (g0) {
+                mma_f16(Z, da0, db0, id_fwd, 0u);
+                mma_f16(Z, da0, db1, id_fwd, 1u);
+                mma_commit(doneZ);
+            }
 #pragma unroll
             for (int ks = 0; ks < 8; ks++) mma_f16(tmem + c.xe1, dam + 128u * ks, dx + 16u * ks, id_n8, ks > 0 ? 1u : acc0);
             mma_commit(doneW);
@@ -278,6 +302,32 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
                 if (dst[u]) *dst[u] = v[u];
         }
     }
+    {   // 16-bit layer-1 weights P1[j] = {W1[j][0..O), b1[j], 0..}, K-major no-swizzle chunks {hi, hi, lo, 0}: with the
+        // input split the same way (x = hi + lo) two K = 16 MMAs give x.hi P.hi + x.lo P.hi + x.hi P.lo, i.e. layer 1 to
+        // ~2^-21 although every operand is 16 bits wide
+        for (int e = tid; e < 2 * TC_H; e += nthreads) {
+            const int net = e >> 6, j = e & 63;
+            float v[8], lo[8], z[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                v[i] = 0.0f;
+                z[i] = 0.0f;
+                if (i < O) v[i] = __ldg(a.params + offs[net].W1 + j * O + i);
+                if (i == O) v[i] = __ldg(a.params + offs[net].b1 + j);
+            }
+#pragma unroll
+            for (int i = 0; i < 8; i += 2) {
+                const uint32_t ph = pack2<FMT>(v[i], v[i + 1]);
+                lo[i] = v[i] - unpack_lo<FMT>(ph);
+                lo[i + 1] = v[i + 1] - unpack_hi<FMT>(ph);
+            }
+            uint8_t* dst = sm + L.p1h[net] + j * 16;
+            store8<FMT>(dst, v);
+            store8<FMT>(dst + TC_H * 16, v);
+            store8<FMT>(dst + 2 * TC_H * 16, lo);
+            store8<FMT>(dst + 3 * TC_H * 16, z);
+        }
+    }
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -341,46 +391,75 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
             }
             return in;
         };
-        RowIn nxt = gather(blockIdx.x * NWG + g);
-        int tiles_done = 0;
-        for (int tile = blockIdx.x * NWG + g; tile < ntiles; tile += nwg_total) {
-            const RowIn cur = nxt;
-            nxt = gather(tile + nwg_total);
-            const bool on = cur.on;
-            const int64_t r = cur.r;
+        // XE row of a tile = {obs, 1, 0..} in 16 bits: A operand of the layer-1 MMA (G0) and B operand of d[W1|b1] (G3b/G4)
+        auto stage_xe = [&](const RowIn& in, int par_) {
             float xe[8];
 #pragma unroll
             for (int i = 0; i < 8; i++) xe[i] = 0.0f;
             if (O <= 4) {
 #pragma unroll
-                for (int i = 0; i < 4; i++) xe[i] = cur.o[i];
-            } else if (on) {
+                for (int i = 0; i < 4; i++) xe[i] = in.o[i];
+            } else if (in.on) {
 #pragma unroll
                 for (int i = 0; i < 7; i++)
-                    if (i < O) xe[i] = __ldg(a.obs + r * O + i);
+                    if (i < O) xe[i] = __ldg(a.obs + in.r * O + i);
             }
 #pragma unroll
             for (int i = 0; i < 8; i++)
                 if (i == O) xe[i] = 1.0f;
-
+            float lo[8];
+#pragma unroll
+            for (int i = 0; i < 8; i += 2) {
+                const uint32_t ph = pack2<FMT>(xe[i], xe[i + 1]);
+                lo[i] = xe[i] - unpack_lo<FMT>(ph);
+                lo[i + 1] = xe[i + 1] - unpack_hi<FMT>(ph);
+            }
+            store8<FMT>(wg + L.xe[par_] + wt * 16, xe);
+            store8<FMT>(wg + L.xe[par_] + TC_ROWS * 16 + wt * 16, lo);
+        };
+        RowIn nxt = gather(blockIdx.x * NWG + g);
+        int tiles_done = 0;
+        if (blockIdx.x * NWG + g < ntiles) {   // G0 of the first tile
+            stage_xe(nxt, 0);
+            fence_async_smem();
+            bar_sync(barid, 128);
+            if (w4 == 0) {
+                issue_stage<FMT, NWG, 4>(D, L, 0, 0, wbars + 0, wbars + 1);
+                issue_stage<FMT, NWG, 4>(D, L, 1, 0, wbars + 2, wbars + 3);
+            }
+        }
+        for (int tile = blockIdx.x * NWG + g; tile < ntiles; tile += nwg_total) {
+            const RowIn cur = nxt;
+            nxt = gather(tile + nwg_total);
+            const bool has_next = tile + nwg_total < ntiles;
+            const bool on = cur.on;
+            const int64_t r = cur.r;
             const int tsb = 8 + tiles_done * 40;
             TC_TS(tsb);
             const int par = tiles_done & 1;      // XE is double-buffered: G3b / G4 of the previous tile may still read it
             tiles_done++;
-            store8<FMT>(wg + L.xe[par] + wt * 16, xe);
             float gvc = 0.0f;                     // critic dL/dvalue of this row (lives from P2 to P3)
 
-            // ---- P1: layer 1 -> A1[net]; G1
+            // ---- P1: h1 = tanh(Z) (G0 = layer-1 pre-activations incl. bias, issued one tile ahead) -> A1[net]; G1
 #pragma unroll 1
             for (int net = 0; net < 2; net++) {
-                const float* P1 = reinterpret_cast<const float*>(sm + L.p1[net]);
                 uint8_t* A1 = wg + L.a1[net];
+                uint64_t* doneZ = wbars + net * 2;
+                mbar_wait(doneZ, pz[net]); pz[net] ^= 1u;
+                tc_fence_after();
+                const uint32_t zaddr = tmem_addr(tmem, (uint32_t)w4 * 32u, (uint32_t)(g * 2 + net) * 64u);
 #pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    float h[8];
-                    layer1_chunk<WIDE>(P1, xe, c * 8, h);
-                    store8<FMT>(A1 + act_chunk_off(wt, c), h);
+                for (int hlf = 0; hlf < 2; hlf++) {
+                    float h[32];
+                    tmem_ld16(zaddr + hlf * 32, h);
+                    tmem_ld16(zaddr + hlf * 32 + 16, h + 16);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; i++) h[i] = tanh_fast(h[i]);
+#pragma unroll
+                    for (int c = 0; c < 4; c++) store8<FMT>(A1 + act_chunk_off(wt, hlf * 4 + c), h + c * 8);
                 }
+                tc_fence_before();
                 fence_async_smem();
                 TC_TS(tsb + 1 + net * 3);
                 bar_sync(barid, 128);
@@ -504,6 +583,7 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
             for (int net = 0; net < 2; net++) {
                 uint8_t *A1 = wg + L.a1[net], *A2 = wg + L.a2[net];
                 uint64_t *doneZ = wbars + net * 2, *doneW = doneZ + 1;
+                if (net == 0 && has_next) stage_xe(nxt, par ^ 1);   // XE[par ^ 1]: last read by the previous tile's G4
                 TC_TS(tsb + 23 + net * 6);
                 mbar_wait(doneZ, pz[net]); pz[net] ^= 1u;
                 tc_fence_after();
@@ -529,7 +609,7 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
                 fence_async_smem();
                 bar_sync(barid, 128);
                 TC_TS(tsb + 27 + net * 6);
-                if (w4 == 0) issue_stage<FMT, NWG, 3>(D, L, net, par, doneZ, doneW);
+                if (w4 == 0) issue_stage<FMT, NWG, 3>(D, L, net, par, doneZ, doneW, has_next);
                 TC_TS(tsb + 28 + net * 6);
             }
             pendingW = true;
