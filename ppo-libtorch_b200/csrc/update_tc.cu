@@ -227,7 +227,7 @@ __device__ __forceinline__ void layer1_chunk(const float* P1, const float (&xe)[
 }
 
 template <int FMT, int NWG, bool WIDE>
-__global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a) {
+__global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const UpdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const int O = a.d.O, K = a.d.K, heads = a.d.heads;
@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
     uint64_t* bars = reinterpret_cast<uint64_t*>(sm + L.bars);  // [(g * 2 + net) * 2 + {doneZ, doneW}]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + L.tmem_slot);
     const int ntiles = (a.mb_size + TC_ROWS - 1) / TC_ROWS;
-    const int nthreads = NWG * 128;
+    const int nthreads = (NWG + 1) * 128;   // NWG compute warpgroups + the MMA-issue warpgroup
     long long* ts_buf = (blockIdx.x == 0 && tid == g_tc_ts_who) ? g_tc_ts : nullptr;
     TC_TS(0);
 
@@ -245,10 +245,11 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
     if (warp == 0) tmem_alloc(tmem_slot, 512);
     if (tid == 0) {
         for (int i = 0; i < NWG * 4; i++) mbar_init(bars + i, 1);   // [(g * 2 + net) * 2 + {doneZ, doneW}]
+        for (int i = 0; i < NWG * 2; i++) mbar_init(bars + NWG * 4 + i, 128);   // ready[g * 2 + net]: operands staged
         mbar_init_fence();
     }
     {   // W2 of both nets as 16-bit activation-layout tiles: 1024 chunk tasks, all loads of a thread in flight together
-        constexpr int W2_IT = (2 * 64 * 8 + NWG * 128 - 1) / (NWG * 128);
+        constexpr int W2_IT = (2 * 64 * 8 + (NWG + 1) * 128 - 1) / ((NWG + 1) * 128);
         float v[W2_IT][8];
 #pragma unroll
         for (int it = 0; it < W2_IT; it++) {
@@ -335,18 +336,69 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
     const uint32_t tmem = *tmem_slot;
     TC_TS(1);
 
+    // ---------------- MMA-issue warpgroup: warp i of it serves compute warpgroup i ---------------------------------
+    // Every tcgen05.mma of these shapes occupies the issue slot for ~58 cycles (measured, tools/umma_time.py), 84 of them
+    // per tile: issued from a compute warp that was ~4900 cycles per tile during which its warpgroup waited at the next
+    // barrier.  Here the compute threads only arrive on ready[net] when a stage's operands are in shared memory; the
+    // issuer replays the fixed stage order.  Registers move from this warpgroup to the compute ones (setmaxnreg).
+    if (warp >= NWG * 4) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        const int g = warp - NWG * 4;
+        if (g < NWG) {
+            WgIssue D;
+            D.wb = smem_u32(sm + L.wg0 + g * L.wg_stride); D.sb = smem_u32(sm); D.tmem = tmem; D.g = g; D.fresh = 0xFFu;
+            uint64_t* wbars = bars + g * 4;
+            uint64_t* ready = bars + NWG * 4 + g * 2;
+            uint32_t pr[2] = {0u, 0u};
+            const int nwg_total = gridDim.x * NWG;
+            int tiles_done = 0;
+            if (blockIdx.x * NWG + g < ntiles) {
+#pragma unroll 1
+                for (int net = 0; net < 2; net++) {
+                    mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
+                    issue_stage<FMT, NWG, 4>(D, L, net, 0, wbars + net * 2, wbars + net * 2 + 1);
+                }
+            }
+            for (int tile = blockIdx.x * NWG + g; tile < ntiles; tile += nwg_total) {
+                const bool has_next = tile + nwg_total < ntiles;
+                const int par = tiles_done & 1;
+                tiles_done++;
+#pragma unroll 1
+                for (int net = 0; net < 2; net++) {
+                    mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
+                    issue_stage<FMT, NWG, 0>(D, L, net, par, wbars + net * 2, wbars + net * 2 + 1);
+                }
+#pragma unroll 1
+                for (int net = 0; net < 2; net++) {
+                    mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
+                    issue_stage<FMT, NWG, 1>(D, L, net, par, wbars + net * 2, wbars + net * 2 + 1);
+                }
+#pragma unroll 1
+                for (int net = 0; net < 2; net++) {
+                    mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
+                    issue_stage<FMT, NWG, 2>(D, L, net, par, wbars + net * 2, wbars + net * 2 + 1);
+                }
+#pragma unroll 1
+                for (int net = 0; net < 2; net++) {
+                    mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
+                    issue_stage<FMT, NWG, 3>(D, L, net, par, wbars + net * 2, wbars + net * 2 + 1, has_next);
+                }
+            }
+        }
+        return;
+    }
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+
     RowSumsF rs;
     float gb3c = 0.0f;  // critic output-bias gradient partial of this thread
     {
         // ---------------- compute warpgroup ------------------------------------------------------------------
         const int g = warp >> 2, wt = tid & 127, w4 = warp & 3;
+        uint64_t* ready = bars + NWG * 4 + g * 2;   // [net]: this stage's operands are staged (128 arrivals)
         uint8_t* wg = sm + L.wg0 + g * L.wg_stride;
         float* x = reinterpret_cast<float*>(wg + L.lg) + wt * L.ldo;     // this row's logits / dL/dlogits
         float* b3acc = reinterpret_cast<float*>(wg + L.b3) + wt * L.ldo; // this thread's actor db3 partials
         for (int q = 0; q < K; q++) b3acc[q] = 0.0f;
-        WgIssue D;
-        D.wb = smem_u32(wg); D.sb = smem_u32(sm); D.tmem = tmem; D.g = g; D.fresh = 0xFFu;
-        const int barid = 1 + g;
         uint64_t* wbars = bars + g * 4;          // [net * 2 + {doneZ, doneW}]
         uint32_t pz[2] = {0u, 0u}, pw[2] = {0u, 0u};
         bool pendingW = false;                   // G4 of the previous tile not yet waited for (both nets)
@@ -422,11 +474,8 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
         if (blockIdx.x * NWG + g < ntiles) {   // G0 of the first tile
             stage_xe(nxt, 0);
             fence_async_smem();
-            bar_sync(barid, 128);
-            if (w4 == 0) {
-                issue_stage<FMT, NWG, 4>(D, L, 0, 0, wbars + 0, wbars + 1);
-                issue_stage<FMT, NWG, 4>(D, L, 1, 0, wbars + 2, wbars + 3);
-            }
+            mbar_arrive(ready + 0);
+            mbar_arrive(ready + 1);
         }
         for (int tile = blockIdx.x * NWG + g; tile < ntiles; tile += nwg_total) {
             const RowIn cur = nxt;
@@ -462,9 +511,8 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
                 tc_fence_before();
                 fence_async_smem();
                 TC_TS(tsb + 1 + net * 3);
-                bar_sync(barid, 128);
+                mbar_arrive(ready + net);
                 TC_TS(tsb + 2 + net * 3);
-                if (w4 == 0) issue_stage<FMT, NWG, 0>(D, L, net, par, wbars + net * 2, wbars + net * 2 + 1);
                 TC_TS(tsb + 3 + net * 3);
             }
             // ---- P2: h2 = tanh(Z + b2) -> A2[net]; output layer; loss; dOut -> DO[net]; G5
@@ -535,9 +583,8 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
                 tc_fence_before();
                 fence_async_smem();
                 TC_TS(tsb + 8 + net * 4);
-                bar_sync(barid, 128);
+                mbar_arrive(ready + net);
                 TC_TS(tsb + 9 + net * 4);
-                if (w4 == 0) issue_stage<FMT, NWG, 1>(D, L, net, par, doneZ, doneW);
                 TC_TS(tsb + 10 + net * 4);
             }
             pendingW = false;
@@ -573,9 +620,8 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
 #pragma unroll
                 for (int c = 0; c < 8; c++) store8<FMT>(A2 + act_chunk_off(wt, c), d + c * 8);
                 fence_async_smem();
-                bar_sync(barid, 128);
+                mbar_arrive(ready + net);
                 TC_TS(tsb + 17 + net * 4);
-                if (w4 == 0) issue_stage<FMT, NWG, 2>(D, L, net, par, doneZ, doneW);
                 TC_TS(tsb + 18 + net * 4);
             }
             // ---- P4: dZ1 = Z * (1 - h1^2) -> A2[net] (once G2 / G3 have read dZ2); G4
@@ -607,9 +653,8 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
                 for (int c = 0; c < 8; c++) store8<FMT>(A2 + act_chunk_off(wt, c), d + c * 8);
                 tc_fence_before();
                 fence_async_smem();
-                bar_sync(barid, 128);
+                mbar_arrive(ready + net);
                 TC_TS(tsb + 27 + net * 6);
-                if (w4 == 0) issue_stage<FMT, NWG, 3>(D, L, net, par, doneZ, doneW, has_next);
                 TC_TS(tsb + 28 + net * 6);
             }
             pendingW = true;
@@ -623,7 +668,7 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
     // ---------------- drain: tensor-memory accumulators -> this CTA's slab (x 1/n), diagnostics ----------------
     TC_TS(2);
     tc_fence_before();
-    __syncthreads();
+    bar_sync(3, NWG * 128);
     TC_TS(3);
     tc_fence_after();
     const int P = num_params(O, TC_H, K);
@@ -706,7 +751,7 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
         red[3 * NT + tid] = (double)rs.kl; red[4 * NT + tid] = (double)rs.clip;
         gbc[tid] = gb3c;
     }
-    __syncthreads();
+    bar_sync(3, NWG * 128);
     // one warp per quantity: lane-strided partial sums, then a fixed xor tree (deterministic)
     if (warp < 5) {
         double acc = 0.0;
@@ -733,7 +778,7 @@ __global__ void __launch_bounds__(NWG * 128, 1) update_tc_kernel(const UpdArgs a
         }
     }
     tc_fence_before();
-    __syncthreads();
+    bar_sync(3, NWG * 128);
     TC_TS(4);
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
@@ -754,7 +799,7 @@ static int launch_tc(const UpdArgs& a, int* grid_out, cudaStream_t st) {
     int grid = (ntiles + NWG - 1) / NWG;
     if (grid > sms) grid = sms;
     if (grid > UPD_MAX_GRID) grid = UPD_MAX_GRID;
-    update_tc_kernel<FMT, NWG, WIDE><<<grid, NWG * 128, smem, st>>>(a);
+    update_tc_kernel<FMT, NWG, WIDE><<<grid, (NWG + 1) * 128, smem, st>>>(a);
     PPO_LAUNCH_CHECK();
     *grid_out = grid;
     return PPO_OK;
