@@ -373,7 +373,10 @@ def run_b200(args, wl_name):
                 " (bf16 cuBLAS sustained)",
                 "flops_per_launch": flops_per_launch, "ms_per_launch": upd_ms_per,
                 "share_of_step": upd_ms / phase_total if phase_total else None}
-    launches = 1 + 1 + 1 + wl["E"] * (2 + wl["MB"] * 3) + 1     # scalars, rollout, gae, per epoch, ev
+    # scalars, rollout, gae, per epoch {permutation, adv moments, per minibatch {update, reduce[+clip+AdamW fused on one
+    # GPU; + NCCL allreduce (not counted: not ours) + clip_adamw under data parallelism]}}, explained variance
+    per_mb = 2 if world == 1 else 3
+    launches = 1 + 1 + 1 + wl["E"] * (2 + wl["MB"] * per_mb) + 1
 
     line = {"metric": "env_steps_per_sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "update.cuh"
 
 namespace ppo {
 int clip_adamw_launch(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_params, float lr,
@@ -329,6 +330,25 @@ static int phase_minibatch_grads(ppo_trainer* t, int mb, cudaStream_t st) {
                                 t->grads, t->grads + t->P, st);
 }
 
+// single-GPU iterations: gradient + reduction + clip + AdamW back to back, the optimiser fused into the reduction launch
+static int phase_minibatch_step(ppo_trainer* t, int mb, cudaStream_t st) {
+    const ppo_trainer_cfg& c = t->cfg;
+    const int64_t start = (int64_t)mb * t->mb_size;
+    int64_t cnt = t->B - start;
+    if (cnt > t->mb_size) cnt = t->mb_size;
+    PPO_REQUIRE(cnt >= 1, "minibatch %d is empty", mb);
+    const int k = t->opt_in_iter++;
+    PPO_REQUIRE(k < t->n_opt, "more optimiser steps than update_epochs * num_minibatches in one iteration");
+    ppo::FuseAdam f{};
+    f.params = t->params; f.exp_avg = t->exp_avg; f.exp_avg_sq = t->exp_avg_sq; f.d_lr = &t->d_scal->lr;
+    f.beta1 = c.beta1; f.beta2 = c.beta2; f.eps = c.adam_eps; f.weight_decay = c.weight_decay;
+    f.step_host = (int64_t)k + 1; f.d_step = &t->d_scal->step_base; f.max_grad_norm = c.max_grad_norm;
+    f.norm_out = t->norm_out; f.diag_hist = t->diag_hist + (size_t)k * 8;
+    return ppo::update_minibatch_fused(t->params, &c.dims, t->obs, t->masks, t->actions, t->logprobs, t->adv, t->ret,
+                                       t->values, t->perm, start, (int)cnt, 1.0f / (float)cnt, t->adv_stats + 2 * mb,
+                                       &c.hyper, t->upd_ws, t->grads, t->grads + t->P, &f, st);
+}
+
 static int phase_apply(ppo_trainer* t, cudaStream_t st) {
     const ppo_trainer_cfg& c = t->cfg;
     PhaseTimer pt(t, PH_APPLY, st);
@@ -361,7 +381,12 @@ static int enqueue_iteration(ppo_trainer* t, cudaStream_t st) {
     if ((rc = phase_rollout(t, st))) return rc;
     for (int e = 0; e < t->cfg.update_epochs; e++) {
         if ((rc = phase_begin_epoch(t, e, st))) return rc;
+        const bool fused = !(t->cfg.world_size > 1 && t->comm) && !t->profile;
         for (int mb = 0; mb < t->n_mb; mb++) {
+            if (fused) {
+                if ((rc = phase_minibatch_step(t, mb, st))) return rc;
+                continue;
+            }
             if ((rc = phase_minibatch_grads(t, mb, st))) return rc;
             if ((rc = phase_apply(t, st))) return rc;
         }

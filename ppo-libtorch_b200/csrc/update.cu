@@ -114,7 +114,6 @@ __global__ void __launch_bounds__(MLP_THREADS) update_kernel(const UpdArgs a) {
 // partials into diag_out = {pg_loss, v_loss, entropy, loss, approx_kl, clipfrac, 0, 0}.
 // A block owns RED_COLS consecutive parameters; its 256 threads split the slabs RED_PARTS ways (coalesced 256-byte
 // rows, independent loads in flight), then combine the RED_PARTS partial sums in fixed order.
-constexpr int RED_COLS = 64, RED_PARTS = 4;
 __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_kernel(
     const float* __restrict__ slabs, const double* __restrict__ dpart, int nslabs, int P, int64_t stride, float inv_n,
     float ent_coef, float vf_coef, float* __restrict__ grads_out, float* __restrict__ diag_out) {
@@ -158,13 +157,167 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_kernel(
         }
     }
 }
-static inline void launch_reduce(const UpdArgs& a, int grid, int P, float* grads_out, float* diag_out, cudaStream_t st) {
-    reduce_kernel<<<(P + RED_COLS - 1) / RED_COLS, RED_COLS * RED_PARTS, 0, st>>>(
+// reduce_kernel + clip_grad_norm_ + AdamW in one launch.  Every CTA reduces its RED_COLS columns as above and leaves the
+// sum of their squares in sq_part[block].  spin (grid <= SM count, so every CTA is resident): each CTA waits until all
+// tickets are taken, adds the partials in block order (the norm is run-to-run identical and the same in every CTA) and
+// applies clip + decoupled weight decay + Adam (optim.cu's arithmetic) to its own columns.  Otherwise the last CTA to
+// take a ticket steps all P parameters.  The ticket pair (arrivals, departures) is re-armed before the kernel ends.
+__global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_apply_kernel(
+    const float* __restrict__ slabs, const double* __restrict__ dpart, int nslabs, int P, int64_t stride, float inv_n,
+    float ent_coef, float vf_coef, float* grads_out, float* __restrict__ diag_out, const FuseAdam f, unsigned* ticket,
+    double* sq_part, const bool spin) {
+    __shared__ double part[RED_PARTS][RED_COLS];
+    __shared__ double shn[RED_COLS * RED_PARTS / 32];
+    __shared__ unsigned s_last;
+    const int col = threadIdx.x & (RED_COLS - 1), pt = threadIdx.x / RED_COLS;
+    const int i = blockIdx.x * RED_COLS + col;
+    double acc = 0.0;
+    if (i < P) {
+        const int per = (nslabs + RED_PARTS - 1) / RED_PARTS;
+        const int s0 = pt * per, s1 = min(nslabs, s0 + per);
+        const float* p = slabs + (size_t)s0 * stride + i;
+        int s = s0;
+        for (; s + 4 <= s1; s += 4, p += 4 * stride) {
+            const float a0 = p[0], a1 = p[stride], a2 = p[2 * stride], a3 = p[3 * stride];
+            acc += (double)a0; acc += (double)a1; acc += (double)a2; acc += (double)a3;
+        }
+        for (; s < s1; s++, p += stride) acc += (double)p[0];
+    }
+    part[pt][col] = acc;
+    __syncthreads();
+    double sq = 0.0;
+    if (pt == 0 && i < P) {
+        double t = part[0][col];
+#pragma unroll
+        for (int q = 1; q < RED_PARTS; q++) t += part[q][col];
+        const float g = (float)t;
+        grads_out[i] = g;
+        sq = (double)g * (double)g;
+    }
+    if (threadIdx.x < RED_COLS) {   // warps 0, 1 hold the columns: fixed xor tree, then warp 0 + warp 1
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        if ((threadIdx.x & 31) == 0) shn[threadIdx.x >> 5] = sq;
+    }
+    if (blockIdx.x == 0 && threadIdx.x >= 64 && threadIdx.x < 96) {   // diagnostics (warp 2 of block 0)
+        const int l = threadIdx.x - 64;
+        double v = 0.0;
+        if (l < 5)
+            for (int s = 0; s < nslabs; s++) v += dpart[(size_t)s * UPD_NDIAG + l];
+        const double n_inv = (double)inv_n;
+        const float pg = (float)(__shfl_sync(0xffffffffu, v, 0) * n_inv);
+        const float vl = 0.5f * (float)(__shfl_sync(0xffffffffu, v, 1) * n_inv);
+        const float en = (float)(__shfl_sync(0xffffffffu, v, 2) * n_inv);
+        const float kl = (float)(__shfl_sync(0xffffffffu, v, 3) * n_inv);
+        const float cf = (float)(__shfl_sync(0xffffffffu, v, 4) * n_inv);
+        if (l < 8) {
+            const float d8[8] = {pg, vl, en, pg - ent_coef * en + vl * vf_coef, kl, cf, 0.0f, 0.0f};
+            float dv = 0.0f;
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+                if (q == l) dv = d8[q];
+            if (diag_out) diag_out[l] = dv;
+            if (f.diag_hist) f.diag_hist[l] = dv;
+        }
+    }
+    __threadfence();   // this thread's grads_out / diagnostics stores are visible device-wide before the ticket is taken
+    __syncthreads();
+    int j0, j1;   // the parameter range this CTA steps
+    if (spin) {
+        // every CTA is resident (grid <= SM count, checked by the launcher): publish, wait for all, step the own columns
+        if (threadIdx.x == 0) {
+            sq_part[blockIdx.x] = shn[0] + shn[1];
+            __threadfence();
+            atomicAdd(ticket, 1u);
+            while (*reinterpret_cast<volatile unsigned*>(ticket) < gridDim.x) __nanosleep(32);
+            __threadfence();
+        }
+        __syncthreads();
+        j0 = blockIdx.x * RED_COLS;
+        j1 = min(P, j0 + RED_COLS);
+    } else {
+        if (threadIdx.x == 0) {
+            sq_part[blockIdx.x] = shn[0] + shn[1];
+            __threadfence();
+            s_last = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+        }
+        __syncthreads();
+        if (!s_last) return;
+        __threadfence();
+        j0 = 0;
+        j1 = P;
+    }
+    // ---- norm (partials added in block order by every stepping CTA alike), clip coefficient, AdamW
+    double ss = 0.0;
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += RED_COLS * RED_PARTS) ss += __ldcg(sq_part + b);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if ((threadIdx.x & 31) == 0) shn[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    double tot = 0.0;
+#pragma unroll
+    for (int w = 0; w < RED_COLS * RED_PARTS / 32; w++) tot += shn[w];
+    const double norm = sqrt(tot);
+    if (threadIdx.x == 0 && blockIdx.x == (spin ? 0 : blockIdx.x) && f.norm_out) *f.norm_out = (float)norm;
+    const double coef = (double)f.max_grad_norm / (norm + 1e-6);
+    const float cf = (f.max_grad_norm > 0.0f && coef < 1.0) ? (float)coef : 1.0f;
+    const float lr = *f.d_lr;
+    const int64_t step = f.step_host + (f.d_step ? *f.d_step : 0);
+    const double b1 = (double)f.beta1, b2 = (double)f.beta2;
+    const double bc1 = 1.0 - pow(b1, (double)step);
+    const double bc2 = 1.0 - pow(b2, (double)step);
+    const float decay = (float)(1.0 - (double)lr * (double)f.weight_decay);
+    const float omb1 = (float)(1.0 - b1), omb2 = (float)(1.0 - b2);
+    const float sq_bc2 = (float)sqrt(bc2);
+    const float neg_step = (float)(-((double)lr / bc1));
+    constexpr int NT = RED_COLS * RED_PARTS, U = 4;
+    for (int jb = j0 + threadIdx.x; jb < j1; jb += NT * U) {   // U independent elements per thread: loads in flight together
+        float g[U], pv[U], mv[U], vv[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int j = jb + u * NT;
+            if (j < j1) { g[u] = __ldcg(grads_out + j); pv[u] = f.params[j]; mv[u] = f.exp_avg[j]; vv[u] = f.exp_avg_sq[j]; }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int j = jb + u * NT;
+            if (j >= j1) continue;
+            float gg = g[u];
+            if (cf != 1.0f) gg = __fmul_rn(gg, cf);
+            const float p = __fmul_rn(pv[u], decay);
+            const float mi = __fadd_rn(__fmul_rn(mv[u], f.beta1), __fmul_rn(gg, omb1));
+            const float vi = __fadd_rn(__fmul_rn(vv[u], f.beta2), __fmul_rn(__fmul_rn(gg, gg), omb2));
+            f.exp_avg[j] = mi;
+            f.exp_avg_sq[j] = vi;
+            const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(vi), sq_bc2), f.eps);
+            f.params[j] = __fadd_rn(p, __fmul_rn(neg_step, __fdiv_rn(mi, denom)));
+        }
+    }
+    // re-arm the ticket for the next launch
+    if (spin) {
+        __syncthreads();
+        if (threadIdx.x == 0 && atomicAdd(ticket + 1, 1u) == gridDim.x - 1) { ticket[0] = 0u; ticket[1] = 0u; }
+    } else if (threadIdx.x == 0) {
+        *ticket = 0u;
+    }
+}
+static inline void launch_reduce(const UpdArgs& a, int grid, int P, float* grads_out, float* diag_out, cudaStream_t st,
+                                 const FuseAdam* fuse = nullptr) {
+    const int blocks = (P + RED_COLS - 1) / RED_COLS;
+    if (fuse) {
+        char* tail = reinterpret_cast<char*>(a.dpart) + (size_t)UPD_MAX_GRID * UPD_NDIAG * sizeof(double);
+        reduce_apply_kernel<<<blocks, RED_COLS * RED_PARTS, 0, st>>>(
+            a.slabs, a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out, *fuse,
+            reinterpret_cast<unsigned*>(tail), reinterpret_cast<double*>(tail + 64),
+            blocks <= (sm_count() > 0 ? sm_count() : 0));
+        return;
+    }
+    reduce_kernel<<<blocks, RED_COLS * RED_PARTS, 0, st>>>(
         a.slabs, a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out);
 }
 
 template <int TM, int H>
-static int launch_update(const UpdArgs& a, float* grads_out, float* diag_out, cudaStream_t st) {
+static int launch_update(const UpdArgs& a, float* grads_out, float* diag_out, cudaStream_t st, const FuseAdam* fuse) {
     const TileLayout L = tile_layout(TM, H, a.d.O, a.d.K);
     const size_t smem = (size_t)(((L.end + 1) & ~1) + 2 * TM) * sizeof(float);
     static bool attr_done = false;
@@ -180,7 +333,7 @@ static int launch_update(const UpdArgs& a, float* grads_out, float* diag_out, cu
     update_kernel<TM, H><<<grid, MLP_THREADS, smem, st>>>(a);
     PPO_LAUNCH_CHECK();
     const int P = num_params(a.d.O, a.d.H, a.d.K);
-    launch_reduce(a, grid, P, grads_out, diag_out, st);
+    launch_reduce(a, grid, P, grads_out, diag_out, st, fuse);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
 }
@@ -193,7 +346,8 @@ extern "C" int64_t ppo_update_workspace_bytes(const ppo_dims* dims) {
     Dims d;
     if (make_dims(dims, &d)) return -1;
     const int P = num_params(d.O, d.H, d.K);
-    return (int64_t)UPD_MAX_GRID * (slab_stride(P) * (int64_t)sizeof(float) + UPD_NDIAG * (int64_t)sizeof(double));
+    return (int64_t)UPD_MAX_GRID * (slab_stride(P) * (int64_t)sizeof(float) + UPD_NDIAG * (int64_t)sizeof(double)) +
+           upd_tail_bytes(P);
 }
 
 extern "C" int ppo_update_minibatch(const float* params, const ppo_dims* dims, const float* obs, const uint8_t* mask,
@@ -201,6 +355,16 @@ extern "C" int ppo_update_minibatch(const float* params, const ppo_dims* dims, c
                                     const float* ret, const float* old_val, const int32_t* perm, int64_t mb_start,
                                     int mb_size, float inv_n, const float* adv_stats, const ppo_hyper* h_hyper,
                                     void* workspace, float* grads_out, float* diag_out, ppo_stream_t stream) {
+    return update_minibatch_fused(params, dims, obs, mask, actions, old_logprob, adv, ret, old_val, perm, mb_start,
+                                  mb_size, inv_n, adv_stats, h_hyper, workspace, grads_out, diag_out, nullptr,
+                                  as_stream(stream));
+}
+
+int ppo::update_minibatch_fused(const float* params, const ppo_dims* dims, const float* obs, const uint8_t* mask,
+                                const int32_t* actions, const float* old_logprob, const float* adv, const float* ret,
+                                const float* old_val, const int32_t* perm, int64_t mb_start, int mb_size, float inv_n,
+                                const float* adv_stats, const ppo_hyper* h_hyper, void* workspace, float* grads_out,
+                                float* diag_out, const FuseAdam* fuse, cudaStream_t st) {
     UpdArgs a{};
     if (int rc = make_dims(dims, &a.d)) return rc;
     PPO_REQUIRE(params && obs && actions && old_logprob && adv && ret && h_hyper && workspace && grads_out,
@@ -216,22 +380,21 @@ extern "C" int ppo_update_minibatch(const float* params, const ppo_dims* dims, c
     a.slabs = reinterpret_cast<float*>(workspace);
     a.dpart = reinterpret_cast<double*>(reinterpret_cast<char*>(workspace) +
                                         (size_t)UPD_MAX_GRID * slab_stride(P) * sizeof(float));
-    cudaStream_t st = as_stream(stream);
     const int mode = math_mode();
     if (mode != PPO_MATH_FP32) {  // tensor-core path when the shape fits its envelope, else the FMA kernels below
         int grid = 0;
         const int rc = launch_update_tc(a, mode == PPO_MATH_BF16 ? 1 : 0, &grid, st);
         if (rc == PPO_OK) {
-            launch_reduce(a, grid, P, grads_out, diag_out, st);
+            launch_reduce(a, grid, P, grads_out, diag_out, st, fuse);
             PPO_LAUNCH_CHECK();
             return PPO_OK;
         }
         if (rc != PPO_ERR_UNSUPPORTED) return rc;
     }
     switch (a.d.H) {
-        case 64: return launch_update<64, 64>(a, grads_out, diag_out, st);
-        case 128: return launch_update<32, 128>(a, grads_out, diag_out, st);
-        case 256: return launch_update<32, 256>(a, grads_out, diag_out, st);
+        case 64: return launch_update<64, 64>(a, grads_out, diag_out, st, fuse);
+        case 128: return launch_update<32, 128>(a, grads_out, diag_out, st, fuse);
+        case 256: return launch_update<32, 256>(a, grads_out, diag_out, st, fuse);
     }
     set_error("hidden=%d unsupported", a.d.H);
     return PPO_ERR_UNSUPPORTED;

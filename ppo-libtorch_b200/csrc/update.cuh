@@ -30,6 +30,30 @@ struct UpdArgs {
     double* dpart;   // [grid][UPD_NDIAG]
 };
 
+// Optional tail of the slab reduction: clip_grad_norm_ + AdamW (PPO/PPO_Discrete.cpp:640-641) applied by the LAST reduce
+// CTA to finish (single-GPU path: no allreduce sits between the gradient and the optimiser, so reduce + norm + step are
+// one launch instead of two).  Workspace tail: ticket (zeroed once, left zeroed) + one double per reduce CTA.
+struct FuseAdam {
+    float* params;
+    float* exp_avg;
+    float* exp_avg_sq;
+    const float* d_lr;
+    float beta1, beta2, eps, weight_decay;
+    int64_t step_host;
+    const int64_t* d_step;
+    float max_grad_norm;
+    float* norm_out;
+    float* diag_hist;   // 8 floats of this optimiser step
+};
+constexpr int RED_COLS = 64, RED_PARTS = 4;
+__host__ __device__ inline int64_t upd_tail_bytes(int P) { return 64 + (int64_t)((P + RED_COLS - 1) / RED_COLS) * 8; }
+// ppo_update_minibatch with the optimiser step fused behind it (trainer.cu)
+int update_minibatch_fused(const float* params, const ppo_dims* dims, const float* obs, const uint8_t* mask,
+                           const int32_t* actions, const float* old_logprob, const float* adv, const float* ret,
+                           const float* old_val, const int32_t* perm, int64_t mb_start, int mb_size, float inv_n,
+                           const float* adv_stats, const ppo_hyper* h_hyper, void* workspace, float* grads_out,
+                           float* diag_out, const FuseAdam* fuse, cudaStream_t st);
+
 // update_tc.cu: returns PPO_ERR_UNSUPPORTED (without touching the error string) when the shape is outside the
 // tensor-core kernel's envelope (hidden != 64, obs_dim > 7, sumK > 32), PPO_OK after launching, else an error.
 int launch_update_tc(const UpdArgs& a, int fmt, int* grid_out, cudaStream_t st);

@@ -577,3 +577,42 @@ def test_trainer_graph_equals_eager(P):
         out.append(tr.get_params())
         tr.close()
     assert np.array_equal(out[0], out[1])
+
+
+@pytest.fixture
+def math_mode(P):
+    prev = P.ops.get_math_mode()
+    yield P.ops.set_math_mode
+    P.ops.set_math_mode(prev)
+
+
+@pytest.mark.parametrize("mode", [0, 2])
+def test_trainer_fused_step_equals_split_phases(P, math_mode, mode):
+    """iterate() on one GPU fuses slab reduction + clip_grad_norm_ + AdamW into one launch (reduce_apply_kernel); the
+    split-phase API keeps them apart (reduce_kernel, clip_adamw_kernel).  Same gradients, same optimiser arithmetic:
+    parameters, Adam moments and the reported diagnostics agree (the two paths add the squared-gradient partials in a
+    different order, hence the last-bit tolerance)."""
+    math_mode(mode)
+    N, T, MB, E, lr = 96, 16, 3, 2, 7e-4
+    a = P.Trainer(num_envs=N, num_steps=T, num_minibatches=MB, update_epochs=E, nvec=(2,), seed=9)
+    b = P.Trainer(num_envs=N, num_steps=T, num_minibatches=MB, update_epochs=E, nvec=(2,), seed=9)
+    for it in range(2):
+        ra = a.iterate(lr)
+        b.rollout(lr)
+        for e in range(E):
+            b.begin_epoch(e)
+            for k in range(MB):
+                b.minibatch_grads(k)
+                b.apply()
+        rb = b.finish(lr)
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(a.get_params(), b.get_params(), rtol=1e-6, atol=1e-8)
+        ma, va, sa = a.get_opt_state()
+        mb_, vb, sb = b.get_opt_state()
+        assert sa == sb == (it + 1) * MB * E
+        np.testing.assert_allclose(ma, mb_, rtol=1e-6, atol=1e-10)
+        np.testing.assert_allclose(va, vb, rtol=1e-6, atol=1e-12)
+        for key in ("pg_loss", "v_loss", "loss", "approx_kl", "clipfrac", "grad_norm", "explained_variance"):
+            np.testing.assert_allclose(ra[key], rb[key], rtol=1e-5, atol=1e-7, err_msg=key)
+    a.close()
+    b.close()
