@@ -32,6 +32,10 @@ WORKLOADS = {
     "cartpole_8x32_h64": dict(env=0, O=4, nvec=(2,), H=64, N=8, T=32, MB=4, E=10, max_ep=500),
 }
 DEFAULT_WORKLOAD = "cartpole_4096x128_h64"
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE update-kernel launch from an `ncu --set full` capture of this
+# command (profiles/r01h_update_tc_kernel_v5_ncu.txt): 18.69 MB + 16 KB.  Algorithmic bytes per launch are 131072 rows x
+# 36 B + the 0.5 MB permutation slice = 5.2 MB: the gather through the permutation pulls a 32 B sector per 4 B field.
+NCU_TRAFFIC = {("cartpole_4096x128_h64", 2): 18.69e6 + 16.1e3}
 HYPER = dict(gamma=0.98, gae_lambda=0.95, clip_coef=0.2, norm_adv=True, clip_vloss=True, ent_coef=0.0, vf_coef=0.5,
              max_grad_norm=0.5)
 LR0 = 1e-3
@@ -369,7 +373,7 @@ def run_b200(args, wl_name):
                  2: "fp16 tcgen05 path (update_tc_kernel)"}[mode]
     roofline = {"bound": "tensor", "kernel": "fused fwd + PPO loss + bwd, " + mode_name,
                 "achieved": achieved_tf, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
-                "frac": achieved_tf / pk["bf16_sustained"], "traffic": None, "peak_source": pk["source"] +
+                "frac": achieved_tf / pk["bf16_sustained"], "traffic": NCU_TRAFFIC.get((wl_name, mode)), "peak_source": pk["source"] +
                 " (bf16 cuBLAS sustained)",
                 "flops_per_launch": flops_per_launch, "ms_per_launch": upd_ms_per,
                 "share_of_step": upd_ms / phase_total if phase_total else None}
