@@ -699,8 +699,19 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
 #pragma unroll
                 for (int k = 0; k < 64; k++) v[k] += w[k];
         }
+        {   // dW2 rows -> slab through a per-warp shared-memory transpose: a thread owns a whole 64-float row, so direct
+            // stores would hit 32 sectors per instruction; staged, every store instruction covers one row segment
+            float* buf = reinterpret_cast<float*>(sm + L.wg0 + (NWG > 1 ? L.wg_stride : 8192)) + warp * (32 * 65);
 #pragma unroll
-        for (int k = 0; k < 64; k++) slab[of.W2 + n * TC_H + k] = v[k] * sc;
+            for (int k = 0; k < 64; k++) buf[lane * 65 + k] = v[k] * sc;
+            __syncwarp();
+#pragma unroll 4
+            for (int r = 0; r < 32; r++) {
+                float* dst = slab + offs[r >> 4].W2 + (16 * warp + (r & 15)) * TC_H;
+                dst[lane] = buf[r * 65 + lane];
+                dst[lane + 32] = buf[r * 65 + lane + 32];
+            }
+        }
         float e[8], f[8];
 #pragma unroll
         for (int g = 0; g < NWG; g++) {
