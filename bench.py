@@ -304,6 +304,15 @@ def run_b200(args, wl_name):
         uid = [P.unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         tr.init_comm(uid[0], rank, world)
+        if not args.no_peer:
+            # gradient exchange over peer memory (one fused kernel per rank) instead of reduce -> NCCL -> clip/AdamW
+            hs = [None] * world
+            dist.all_gather_object(hs, tr.peer_handle())
+            try:
+                tr.set_peers(hs)
+            except P.PpoError as e:
+                if rank == 0:
+                    print("peer-memory path unavailable, NCCL path in use:", e, file=sys.stderr)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
     K, W = args.steps, args.warmup
@@ -379,7 +388,7 @@ def run_b200(args, wl_name):
                 "share_of_step": upd_ms / phase_total if phase_total else None}
     # scalars, rollout, gae, per epoch {permutation, adv moments, per minibatch {update, reduce[+clip+AdamW fused on one
     # GPU; + NCCL allreduce (not counted: not ours) + clip_adamw under data parallelism]}}, explained variance
-    per_mb = 2 if world == 1 else 3
+    per_mb = 2 if (world == 1 or not args.no_peer) else 3
     launches = 1 + 1 + 1 + wl["E"] * (2 + wl["MB"] * per_mb) + 1
 
     line = {"metric": "env_steps_per_sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K,
@@ -387,7 +396,8 @@ def run_b200(args, wl_name):
             "dtype": {0: "f32", 1: "bf16", 2: "f16"}[mode], "data": "synthetic",
             "config": {"workload": wl_name, "env": "CartPole" if wl["env"] == 0 else "MountainCar",
                        "envs_per_gpu": wl["N"], "rollout_steps": wl["T"], "hidden": wl["H"], "update_epochs": wl["E"],
-                       "minibatches": wl["MB"], "global_batch": batch * world, "parallelism": f"dp{world}",
+                       "minibatches": wl["MB"], "global_batch": batch * world, "parallelism": f"dp{world}", "grad_exchange": "none" if world == 1 else (
+                           "nccl" if args.no_peer else "peer-memory fused reduce+AdamW (NVLink P2P)"),
                        "l2": "flushed between steps (256 MiB write, untimed)", "cuda_graph": not args.no_graph,
                        "policy": "orthogonal-init weights, live-sampled actions"},
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": 32,
@@ -420,6 +430,7 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of CUDA-graph replay")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-peer", action="store_true", help="N>1: NCCL gradient allreduce instead of the peer-memory kernel")
     ap.add_argument("--no-kernels", action="store_true", help="skip the stand-alone kernel rooflines")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

@@ -298,6 +298,15 @@ int ppo_comm_rank(const ppo_comm* c);
 int ppo_comm_allreduce_f32(ppo_comm* c, float* buf, int64_t count, ppo_stream_t stream);
 int ppo_comm_allreduce_f64(ppo_comm* c, double* buf, int64_t count, ppo_stream_t stream);
 int ppo_trainer_set_comm(ppo_trainer* t, ppo_comm* comm);
+/* Peer-memory gradient exchange over NVLink (replaces reduce -> ncclAllReduce -> clip/AdamW by ONE kernel per rank that
+ * publishes its reduced gradient blocks, reads the peers' blocks with P2P loads, sums them in rank order and applies
+ * clip + AdamW: csrc/update.cu reduce_peer_apply_kernel).  Each rank exports a 64-byte CUDA IPC handle of its exchange
+ * buffer; the launcher gathers the world_size handles (rank order) and hands all of them to every rank.  After
+ * ppo_trainer_set_peers, ppo_trainer_iterate uses the peer path (the per-epoch advantage moments still go through the
+ * communicator set with ppo_trainer_set_comm).  PPO_ERR_UNSUPPORTED: parameter count too large for the single-wave
+ * kernel (the NCCL path stays in use). */
+int ppo_trainer_peer_handle(ppo_trainer* t, char* h_handle64);
+int ppo_trainer_set_peers(ppo_trainer* t, const char* h_handles, int world_size);
 
 /* ---- diagnostics ----------------------------------------------------------------------------- */
 /* Known-answer probe of the tcgen05 (16-bit operands, fp32 TMEM accumulator) building blocks the fused kernels

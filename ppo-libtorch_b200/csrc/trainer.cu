@@ -41,6 +41,7 @@ struct Scalars {           // device scalars a captured graph reads
 struct Readback {          // one D2H per iteration
     float ev, grad_norm;
     double ep_stats[3];
+    unsigned peer_err, pad;
 };
 }  // namespace
 
@@ -73,6 +74,10 @@ struct ppo_trainer {
     cudaGraphExec_t graph_exec = nullptr;
     cudaStream_t graph_stream = nullptr;
     int opt_in_iter = 0;  // optimiser steps issued in the current iteration (split-phase API)
+    // peer-memory gradient exchange (update.cuh: PeerArgs): own exchange buffer + the peers' IPC mappings
+    char* xchg = nullptr;
+    ppo::PeerArgs peer{};
+    bool peer_ready = false;
     // optional per-phase device timing (cudaEvent pairs on the launch stream; eager mode only)
     bool profile = false;
     std::vector<cudaEvent_t> ev_pool;
@@ -114,6 +119,9 @@ extern "C" void ppo_trainer_destroy(ppo_trainer* t) {
     if (!t) return;
     if (t->graph_exec) cudaGraphExecDestroy(t->graph_exec);
     for (cudaEvent_t e : t->ev_pool) cudaEventDestroy(e);
+    for (int r = 0; r < ppo::PEER_MAX; r++)
+        if (t->peer_ready && r != t->peer.rank && t->peer.xchg[r]) cudaIpcCloseMemHandle(t->peer.xchg[r]);
+    if (t->xchg) cudaFree(t->xchg);
     if (t->arena) cudaFree(t->arena);
     if (t->h_diag) cudaFreeHost(t->h_diag);
     if (t->h_rb) cudaFreeHost(t->h_rb);
@@ -206,6 +214,51 @@ extern "C" ppo_trainer* ppo_trainer_create(const ppo_trainer_cfg* c) {
     }
     cudaDeviceSynchronize();
     return t;
+}
+
+// ---- peer-memory gradient exchange: CUDA IPC plumbing ---------------------------------------------------------------
+static size_t xchg_bytes(const ppo_trainer* t) { return 2 * (size_t)ppo::peer_slot_bytes(t->P) + 256; }
+
+extern "C" int ppo_trainer_peer_handle(ppo_trainer* t, char* h_handle64) {
+    PPO_REQUIRE(t && h_handle64, "ppo_trainer_peer_handle: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    if (!t->xchg) {
+        PPO_CUDA(cudaMalloc(&t->xchg, xchg_bytes(t)));
+        PPO_CUDA(cudaMemset(t->xchg, 0, xchg_bytes(t)));
+        PPO_CUDA(cudaDeviceSynchronize());
+    }
+    cudaIpcMemHandle_t h;
+    PPO_CUDA(cudaIpcGetMemHandle(&h, t->xchg));
+    memcpy(h_handle64, &h, 64);
+    return PPO_OK;
+}
+
+extern "C" int ppo_trainer_set_peers(ppo_trainer* t, const char* h_handles, int world) {
+    PPO_REQUIRE(t && h_handles, "ppo_trainer_set_peers: null argument");
+    PPO_REQUIRE(world == t->cfg.world_size && world >= 2 && world <= ppo::PEER_MAX,
+                "ppo_trainer_set_peers: world=%d (cfg.world_size=%d, at most %d)", world, t->cfg.world_size, ppo::PEER_MAX);
+    PPO_REQUIRE(t->xchg, "ppo_trainer_set_peers: call ppo_trainer_peer_handle first");
+    PPO_REQUIRE(!t->peer_ready, "ppo_trainer_set_peers: peers already set");
+    const int blocks = (t->P + ppo::RED_COLS - 1) / ppo::RED_COLS;
+    if (blocks > ppo::PEER_NB || blocks > sm_count()) {
+        set_error("peer-memory exchange supports up to %d parameters on this device; NCCL path stays in use",
+                  (sm_count() < ppo::PEER_NB ? sm_count() : ppo::PEER_NB) * ppo::RED_COLS);
+        return PPO_ERR_UNSUPPORTED;
+    }
+    t->peer.world = world;
+    t->peer.rank = t->cfg.rank;
+    for (int r = 0; r < world; r++) {
+        if (r == t->cfg.rank) { t->peer.xchg[r] = t->xchg; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, h_handles + (size_t)r * 64, 64);
+        void* p = nullptr;
+        PPO_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        t->peer.xchg[r] = (char*)p;
+    }
+    t->peer.err = reinterpret_cast<unsigned*>(t->xchg + 2 * (size_t)ppo::peer_slot_bytes(t->P));
+    t->peer_ready = true;
+    if (t->graph_exec) { cudaGraphExecDestroy(t->graph_exec); t->graph_exec = nullptr; }
+    return PPO_OK;
 }
 
 extern "C" int ppo_trainer_set_comm(ppo_trainer* t, ppo_comm* comm) {
@@ -344,9 +397,11 @@ static int phase_minibatch_step(ppo_trainer* t, int mb, cudaStream_t st) {
     f.beta1 = c.beta1; f.beta2 = c.beta2; f.eps = c.adam_eps; f.weight_decay = c.weight_decay;
     f.step_host = (int64_t)k + 1; f.d_step = &t->d_scal->step_base; f.max_grad_norm = c.max_grad_norm;
     f.norm_out = t->norm_out; f.diag_hist = t->diag_hist + (size_t)k * 8;
+    const bool peer = c.world_size > 1;   // caller checked peer_ready
     return ppo::update_minibatch_fused(t->params, &c.dims, t->obs, t->masks, t->actions, t->logprobs, t->adv, t->ret,
-                                       t->values, t->perm, start, (int)cnt, 1.0f / (float)cnt, t->adv_stats + 2 * mb,
-                                       &c.hyper, t->upd_ws, t->grads, t->grads + t->P, &f, st);
+                                       t->values, t->perm, start, (int)cnt, 1.0f / ((float)cnt * (float)c.world_size),
+                                       t->adv_stats + 2 * mb, &c.hyper, t->upd_ws, t->grads, t->grads + t->P, &f, st,
+                                       peer ? &t->peer : nullptr);
 }
 
 static int phase_apply(ppo_trainer* t, cudaStream_t st) {
@@ -372,6 +427,7 @@ static int phase_tail(ppo_trainer* t, cudaStream_t st) {
     PPO_CUDA(cudaMemcpyAsync(&t->h_rb->ev, t->ev_out, 4, cudaMemcpyDeviceToHost, st));
     PPO_CUDA(cudaMemcpyAsync(&t->h_rb->grad_norm, t->norm_out, 4, cudaMemcpyDeviceToHost, st));
     PPO_CUDA(cudaMemcpyAsync(t->h_rb->ep_stats, t->ep_stats, 24, cudaMemcpyDeviceToHost, st));
+    if (t->peer_ready) PPO_CUDA(cudaMemcpyAsync(&t->h_rb->peer_err, t->peer.err, 4, cudaMemcpyDeviceToHost, st));
     return PPO_OK;
 }
 
@@ -381,7 +437,8 @@ static int enqueue_iteration(ppo_trainer* t, cudaStream_t st) {
     if ((rc = phase_rollout(t, st))) return rc;
     for (int e = 0; e < t->cfg.update_epochs; e++) {
         if ((rc = phase_begin_epoch(t, e, st))) return rc;
-        const bool fused = !(t->cfg.world_size > 1 && t->comm) && !t->profile;
+        const bool dp = t->cfg.world_size > 1 && t->comm;
+        const bool fused = (!dp || t->peer_ready) && !t->profile;
         for (int mb = 0; mb < t->n_mb; mb++) {
             if (fused) {
                 if ((rc = phase_minibatch_step(t, mb, st))) return rc;
@@ -446,6 +503,10 @@ extern "C" int ppo_trainer_iterate(ppo_trainer* t, float h_lr, ppo_iter_result* 
     if (h_result) {
         PPO_CUDA(cudaStreamSynchronize(st));
         fill_result(t, h_lr, h_result);
+        if (t->peer_ready && t->h_rb->peer_err) {
+            set_error("peer-memory gradient exchange: a rank did not publish its gradient block within the spin limit");
+            return PPO_ERR_COMM;
+        }
     }
     return PPO_OK;
 }

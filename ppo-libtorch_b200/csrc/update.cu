@@ -301,9 +301,169 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_apply_kernel(
         *ticket = 0u;
     }
 }
+// ---- data-parallel tail over peer memory (see PeerArgs in update.cuh) ------------------------------------------------
+__device__ __forceinline__ unsigned ld_sys_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ld_sys_f32(const float* p) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_sys_u32(unsigned* p, unsigned v) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel(
+    const float* __restrict__ slabs, const double* __restrict__ dpart, int nslabs, int P, int64_t stride, float inv_n,
+    float ent_coef, float vf_coef, float* grads_out, float* __restrict__ diag_out, const FuseAdam f, const PeerArgs pa,
+    unsigned* ticket, double* sq_part) {
+    __shared__ double part[RED_PARTS][RED_COLS];
+    __shared__ double shn[RED_COLS * RED_PARTS / 32];
+    const int col = threadIdx.x & (RED_COLS - 1), pt = threadIdx.x / RED_COLS;
+    const int i = blockIdx.x * RED_COLS + col;
+    const int64_t step = f.step_host + (f.d_step ? *f.d_step : 0);
+    const unsigned seq = (unsigned)step;
+    const int64_t px = peer_px(P);
+    const int64_t slot_off = (int64_t)(seq & 1u) * peer_slot_bytes(P);
+    float* my_data = reinterpret_cast<float*>(pa.xchg[pa.rank] + slot_off);
+    unsigned* my_flags = reinterpret_cast<unsigned*>(pa.xchg[pa.rank] + slot_off + px * 4);
+    double acc = 0.0;
+    if (i < P) {
+        const int per = (nslabs + RED_PARTS - 1) / RED_PARTS;
+        const int s0 = pt * per, s1 = min(nslabs, s0 + per);
+        const float* p = slabs + (size_t)s0 * stride + i;
+        int s = s0;
+        for (; s + 4 <= s1; s += 4, p += 4 * stride) {
+            const float a0 = p[0], a1 = p[stride], a2 = p[2 * stride], a3 = p[3 * stride];
+            acc += (double)a0; acc += (double)a1; acc += (double)a2; acc += (double)a3;
+        }
+        for (; s < s1; s++, p += stride) acc += (double)p[0];
+    }
+    part[pt][col] = acc;
+    __syncthreads();
+    // ---- publish this rank's column block (and, from block 0, its 8 diagnostics)
+    if (pt == 0 && i < P) {
+        double t = part[0][col];
+#pragma unroll
+        for (int q = 1; q < RED_PARTS; q++) t += part[q][col];
+        my_data[i] = (float)t;
+    }
+    if (blockIdx.x == 0 && threadIdx.x >= 64 && threadIdx.x < 96) {
+        const int l = threadIdx.x - 64;
+        double v = 0.0;
+        if (l < 5)
+            for (int s = 0; s < nslabs; s++) v += dpart[(size_t)s * UPD_NDIAG + l];
+        const double n_inv = (double)inv_n;
+        const float pg = (float)(__shfl_sync(0xffffffffu, v, 0) * n_inv);
+        const float vl = 0.5f * (float)(__shfl_sync(0xffffffffu, v, 1) * n_inv);
+        const float en = (float)(__shfl_sync(0xffffffffu, v, 2) * n_inv);
+        const float kl = (float)(__shfl_sync(0xffffffffu, v, 3) * n_inv);
+        const float cf = (float)(__shfl_sync(0xffffffffu, v, 4) * n_inv);
+        if (l < 8) {
+            const float d8[8] = {pg, vl, en, pg - ent_coef * en + vl * vf_coef, kl, cf, 0.0f, 0.0f};
+            float dv = 0.0f;
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+                if (q == l) dv = d8[q];
+            my_data[px - 64 + l] = dv;
+        }
+    }
+    // release: the CTA barrier orders every thread's data stores before thread 0's system-scope fence (fences are
+    // cumulative), so ONE fence per CTA publishes the block - a fence per thread cost ~10 us per launch
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        st_sys_u32(my_flags + blockIdx.x, seq);
+    }
+    // ---- wait for the same block of every peer (bounded spin: a missing peer sets *err instead of hanging the GPU)
+    if (threadIdx.x < pa.world && threadIdx.x != pa.rank) {
+        const unsigned* pf = reinterpret_cast<const unsigned*>(pa.xchg[threadIdx.x] + slot_off + px * 4) + blockIdx.x;
+        const long long t0 = clock64();
+        while ((int)(ld_sys_u32(pf) - seq) < 0) {
+            if (clock64() - t0 > 4000000000ll) { atomicExch(pa.err, 1u); break; }
+        }
+        __threadfence_system();   // acquire side: only the polling threads, then the barrier hands it to the CTA
+    }
+    __syncthreads();
+    // ---- totals in rank order
+    double sq = 0.0;
+    if (pt == 0 && i < P) {
+        float g = 0.0f;
+        for (int r = 0; r < pa.world; r++) g += ld_sys_f32(reinterpret_cast<const float*>(pa.xchg[r] + slot_off) + i);
+        grads_out[i] = g;
+        sq = (double)g * (double)g;
+    }
+    if (blockIdx.x == 0 && threadIdx.x >= 64 && threadIdx.x < 72) {
+        const int l = threadIdx.x - 64;
+        float dv = 0.0f;
+        for (int r = 0; r < pa.world; r++)
+            dv += ld_sys_f32(reinterpret_cast<const float*>(pa.xchg[r] + slot_off) + px - 64 + l);
+        if (diag_out) diag_out[l] = dv;
+        if (f.diag_hist) f.diag_hist[l] = dv;
+    }
+    if (threadIdx.x < RED_COLS) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        if ((threadIdx.x & 31) == 0) shn[threadIdx.x >> 5] = sq;
+    }
+    __threadfence();
+    __syncthreads();
+    // ---- intra-GPU: every CTA is resident (launcher checks): publish the partial norm, wait for all, step own columns
+    if (threadIdx.x == 0) {
+        sq_part[blockIdx.x] = shn[0] + shn[1];
+        __threadfence();
+        atomicAdd(ticket, 1u);
+        while (*reinterpret_cast<volatile unsigned*>(ticket) < gridDim.x) __nanosleep(32);
+        __threadfence();
+    }
+    __syncthreads();
+    double ss = 0.0;
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += RED_COLS * RED_PARTS) ss += __ldcg(sq_part + b);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if ((threadIdx.x & 31) == 0) shn[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    double tot = 0.0;
+#pragma unroll
+    for (int w = 0; w < RED_COLS * RED_PARTS / 32; w++) tot += shn[w];
+    const double norm = sqrt(tot);
+    if (threadIdx.x == 0 && blockIdx.x == 0 && f.norm_out) *f.norm_out = (float)norm;
+    const double coef = (double)f.max_grad_norm / (norm + 1e-6);
+    const float cf = (f.max_grad_norm > 0.0f && coef < 1.0) ? (float)coef : 1.0f;
+    const float lr = *f.d_lr;
+    const double b1 = (double)f.beta1, b2 = (double)f.beta2;
+    const double bc1 = 1.0 - pow(b1, (double)step);
+    const double bc2 = 1.0 - pow(b2, (double)step);
+    const float decay = (float)(1.0 - (double)lr * (double)f.weight_decay);
+    const float omb1 = (float)(1.0 - b1), omb2 = (float)(1.0 - b2);
+    const float sq_bc2 = (float)sqrt(bc2);
+    const float neg_step = (float)(-((double)lr / bc1));
+    if (pt == 0 && i < P) {
+        float gg = grads_out[i];
+        if (cf != 1.0f) gg = __fmul_rn(gg, cf);
+        const float p = __fmul_rn(f.params[i], decay);
+        const float mi = __fadd_rn(__fmul_rn(f.exp_avg[i], f.beta1), __fmul_rn(gg, omb1));
+        const float vi = __fadd_rn(__fmul_rn(f.exp_avg_sq[i], f.beta2), __fmul_rn(__fmul_rn(gg, gg), omb2));
+        f.exp_avg[i] = mi;
+        f.exp_avg_sq[i] = vi;
+        const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(vi), sq_bc2), f.eps);
+        f.params[i] = __fadd_rn(p, __fmul_rn(neg_step, __fdiv_rn(mi, denom)));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(ticket + 1, 1u) == gridDim.x - 1) { ticket[0] = 0u; ticket[1] = 0u; }
+}
 static inline void launch_reduce(const UpdArgs& a, int grid, int P, float* grads_out, float* diag_out, cudaStream_t st,
-                                 const FuseAdam* fuse = nullptr) {
+                                 const FuseAdam* fuse = nullptr, const PeerArgs* peer = nullptr) {
     const int blocks = (P + RED_COLS - 1) / RED_COLS;
+    if (fuse && peer) {
+        char* tail = reinterpret_cast<char*>(a.dpart) + (size_t)UPD_MAX_GRID * UPD_NDIAG * sizeof(double);
+        reduce_peer_apply_kernel<<<blocks, RED_COLS * RED_PARTS, 0, st>>>(
+            a.slabs, a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out, *fuse,
+            *peer, reinterpret_cast<unsigned*>(tail), reinterpret_cast<double*>(tail + 64));
+        return;
+    }
     if (fuse) {
         char* tail = reinterpret_cast<char*>(a.dpart) + (size_t)UPD_MAX_GRID * UPD_NDIAG * sizeof(double);
         reduce_apply_kernel<<<blocks, RED_COLS * RED_PARTS, 0, st>>>(
@@ -317,7 +477,8 @@ static inline void launch_reduce(const UpdArgs& a, int grid, int P, float* grads
 }
 
 template <int TM, int H>
-static int launch_update(const UpdArgs& a, float* grads_out, float* diag_out, cudaStream_t st, const FuseAdam* fuse) {
+static int launch_update(const UpdArgs& a, float* grads_out, float* diag_out, cudaStream_t st, const FuseAdam* fuse,
+                         const PeerArgs* peer) {
     const TileLayout L = tile_layout(TM, H, a.d.O, a.d.K);
     const size_t smem = (size_t)(((L.end + 1) & ~1) + 2 * TM) * sizeof(float);
     static bool attr_done = false;
@@ -333,7 +494,7 @@ static int launch_update(const UpdArgs& a, float* grads_out, float* diag_out, cu
     update_kernel<TM, H><<<grid, MLP_THREADS, smem, st>>>(a);
     PPO_LAUNCH_CHECK();
     const int P = num_params(a.d.O, a.d.H, a.d.K);
-    launch_reduce(a, grid, P, grads_out, diag_out, st, fuse);
+    launch_reduce(a, grid, P, grads_out, diag_out, st, fuse, peer);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
 }
@@ -364,8 +525,14 @@ int ppo::update_minibatch_fused(const float* params, const ppo_dims* dims, const
                                 const int32_t* actions, const float* old_logprob, const float* adv, const float* ret,
                                 const float* old_val, const int32_t* perm, int64_t mb_start, int mb_size, float inv_n,
                                 const float* adv_stats, const ppo_hyper* h_hyper, void* workspace, float* grads_out,
-                                float* diag_out, const FuseAdam* fuse, cudaStream_t st) {
+                                float* diag_out, const FuseAdam* fuse, cudaStream_t st, const PeerArgs* peer) {
     UpdArgs a{};
+    if (peer) {
+        Dims dd;
+        if (int rc = make_dims(dims, &dd)) return rc;
+        PPO_REQUIRE(fuse && (num_params(dd.O, dd.H, dd.K) + RED_COLS - 1) / RED_COLS <= min(PEER_NB, sm_count()),
+                    "peer-memory reduction needs the fused optimiser and a grid no larger than the SM count");
+    }
     if (int rc = make_dims(dims, &a.d)) return rc;
     PPO_REQUIRE(params && obs && actions && old_logprob && adv && ret && h_hyper && workspace && grads_out,
                 "ppo_update_minibatch: null buffer");
@@ -385,16 +552,16 @@ int ppo::update_minibatch_fused(const float* params, const ppo_dims* dims, const
         int grid = 0;
         const int rc = launch_update_tc(a, mode == PPO_MATH_BF16 ? 1 : 0, &grid, st);
         if (rc == PPO_OK) {
-            launch_reduce(a, grid, P, grads_out, diag_out, st, fuse);
+            launch_reduce(a, grid, P, grads_out, diag_out, st, fuse, peer);
             PPO_LAUNCH_CHECK();
             return PPO_OK;
         }
         if (rc != PPO_ERR_UNSUPPORTED) return rc;
     }
     switch (a.d.H) {
-        case 64: return launch_update<64, 64>(a, grads_out, diag_out, st, fuse);
-        case 128: return launch_update<32, 128>(a, grads_out, diag_out, st, fuse);
-        case 256: return launch_update<32, 256>(a, grads_out, diag_out, st, fuse);
+        case 64: return launch_update<64, 64>(a, grads_out, diag_out, st, fuse, peer);
+        case 128: return launch_update<32, 128>(a, grads_out, diag_out, st, fuse, peer);
+        case 256: return launch_update<32, 256>(a, grads_out, diag_out, st, fuse, peer);
     }
     set_error("hidden=%d unsupported", a.d.H);
     return PPO_ERR_UNSUPPORTED;

@@ -45,6 +45,21 @@ struct FuseAdam {
     float* norm_out;
     float* diag_hist;   // 8 floats of this optimiser step
 };
+// Data-parallel variant of the fused tail: the allreduce happens INSIDE the reduction kernel over peer memory (NVLink
+// P2P loads of the other ranks' exchange buffers, mapped with CUDA IPC), so gradient exchange + clip + AdamW is one launch
+// per rank instead of reduce_kernel -> ncclAllReduce -> clip_adamw_kernel.  Exchange buffer of a rank (one cudaMalloc):
+// two slots (optimiser step parity), each {data[PEER_PX(P)] floats, flags[PEER_NB] uint32}: CTA b publishes its 64 reduced
+// columns into data and then stores the step number into flags[b] (system-scope release); it waits until flags[b] of
+// every peer reached the step, sums the W column blocks in rank order (=> bit-identical totals on every rank) and goes on
+// as the single-GPU kernel.  Slot reuse two steps later is safe: a peer publishes step s+1 only after its step-s reads.
+constexpr int PEER_MAX = 8, PEER_NB = 256;
+__host__ __device__ inline int64_t peer_px(int P) { return (((int64_t)P + 63) & ~(int64_t)63) + 64; }   // + diagnostics
+__host__ __device__ inline int64_t peer_slot_bytes(int P) { return peer_px(P) * 4 + PEER_NB * 4; }
+struct PeerArgs {
+    int world, rank;
+    char* xchg[PEER_MAX];   // every rank's exchange buffer as mapped in THIS process (xchg[rank] = the local one)
+    unsigned* err;          // device flag set when a peer did not arrive within the spin limit
+};
 constexpr int RED_COLS = 64, RED_PARTS = 4;
 __host__ __device__ inline int64_t upd_tail_bytes(int P) { return 64 + (int64_t)((P + RED_COLS - 1) / RED_COLS) * 8; }
 // ppo_update_minibatch with the optimiser step fused behind it (trainer.cu)
@@ -52,7 +67,7 @@ int update_minibatch_fused(const float* params, const ppo_dims* dims, const floa
                            const int32_t* actions, const float* old_logprob, const float* adv, const float* ret,
                            const float* old_val, const int32_t* perm, int64_t mb_start, int mb_size, float inv_n,
                            const float* adv_stats, const ppo_hyper* h_hyper, void* workspace, float* grads_out,
-                           float* diag_out, const FuseAdam* fuse, cudaStream_t st);
+                           float* diag_out, const FuseAdam* fuse, cudaStream_t st, const PeerArgs* peer = nullptr);
 
 // update_tc.cu: returns PPO_ERR_UNSUPPORTED (without touching the error string) when the shape is outside the
 // tensor-core kernel's envelope (hidden != 64, obs_dim > 7, sumK > 32), PPO_OK after launching, else an error.

@@ -130,6 +130,18 @@ class Trainer:
         self.comm = C.c_void_p(h)
         check(load().ppo_trainer_set_comm(self.h, self.comm))
 
+    def peer_handle(self):
+        """64-byte CUDA IPC handle of this rank's gradient exchange buffer"""
+        buf = C.create_string_buffer(64)
+        check(load().ppo_trainer_peer_handle(self.h, buf))
+        return buf.raw
+
+    def set_peers(self, handles):
+        """handles: list of every rank's peer_handle() in rank order -> gradient exchange over peer memory"""
+        blob = b"".join(handles)
+        assert len(blob) == 64 * len(handles)
+        check(load().ppo_trainer_set_peers(self.h, blob, len(handles)))
+
     # -- one PPO iteration (train() loop body)
     def _graph_stream(self, stream):
         """stream capture cannot run on the legacy default stream: route graph replay through a side stream
