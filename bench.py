@@ -386,10 +386,13 @@ def run_b200(args, wl_name):
                 " (bf16 cuBLAS sustained)",
                 "flops_per_launch": flops_per_launch, "ms_per_launch": upd_ms_per,
                 "share_of_step": upd_ms / phase_total if phase_total else None}
-    # scalars, rollout, gae, per epoch {permutation, adv moments, per minibatch {update, reduce[+clip+AdamW fused on one
-    # GPU; + NCCL allreduce (not counted: not ours) + clip_adamw under data parallelism]}}, explained variance
-    per_mb = 2 if (world == 1 or not args.no_peer) else 3
-    launches = 1 + 1 + 1 + wl["E"] * (2 + wl["MB"] * per_mb) + 1
+    # one GPU / peer-memory DP: scalars, rollout, gae, all-epoch advantage statistics, per minibatch {update,
+    # reduce+clip+AdamW}, explained variance.  NCCL DP: per epoch {permutation, moments, finalize}, per minibatch
+    # {update, reduce, clip_adamw} (NCCL's own kernels are not counted: not ours).
+    if world == 1 or not args.no_peer:
+        launches = 4 + wl["E"] * wl["MB"] * 2 + 1 + (1 if world > 1 else 0)
+    else:
+        launches = 3 + wl["E"] * (3 + wl["MB"] * 3) + 1
 
     line = {"metric": "env_steps_per_sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

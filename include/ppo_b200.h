@@ -174,6 +174,13 @@ int64_t ppo_adv_stats_workspace_bytes(int n_mb);
 int ppo_adv_stats(const float* adv, const int32_t* perm, int64_t batch, int mb_size, int n_mb,
                   float* stats_out, double* partial_out, void* workspace, ppo_stream_t stream);
 int ppo_adv_stats_finalize(const double* partial, int n_mb, float* stats_out, ppo_stream_t stream);
+/* The same statistics for all n_epochs x n_mb minibatches of one PPO update in ONE launch (the advantages are fixed
+ * during the update, PPO/PPO_Discrete.cpp:567-594, and the permutation of epoch e is ppo_make_permutation(batch, seed,
+ * epoch0 + e [+ *d_epoch]) evaluated inline, no index buffer).  stats_out [n_epochs*n_mb, 2] and / or partial_out
+ * [n_epochs*n_mb, 3]; workspace: ppo_adv_stats_workspace_bytes(n_epochs * n_mb) bytes, zeroed once. */
+int ppo_adv_stats_all_epochs(const float* adv, int64_t batch, int mb_size, int n_mb, int n_epochs, uint64_t seed,
+                             uint64_t epoch0, const uint64_t* d_epoch, float* stats_out, double* partial_out,
+                             void* workspace, ppo_stream_t stream);
 /* Scratch the update kernel needs: returns bytes for `workspace`. */
 int64_t ppo_update_workspace_bytes(const ppo_dims* dims);
 /* PPO/PPO_Discrete.cpp:579-638 for the minibatch rows perm[mb_start .. mb_start+mb_size):

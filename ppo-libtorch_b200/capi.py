@@ -73,6 +73,8 @@ _PROTOS = {
     "ppo_abi_version": (C.c_int, []),
     "ppo_set_math_mode": (C.c_int, [C.c_int]),
     "ppo_get_math_mode": (C.c_int, []),
+    "ppo_adv_stats_all_epochs": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint64,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ppo_trainer_peer_handle": (C.c_int, [C.c_void_p, C.c_char_p]),
     "ppo_trainer_set_peers": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "ppo_debug_rollout_impl": (C.c_int, [C.c_int]),

@@ -101,6 +101,42 @@ struct Philox {
 // stream ids so that resets, sampling and permutations never share a counter
 enum { RNG_STREAM_RESET = 1, RNG_STREAM_SAMPLE = 2 };
 
+// Permutation of [0, batch) (replaces torch::randperm, PPO/PPO_Discrete.cpp:569): a 4-round Feistel network on the
+// smallest even-width bit domain that covers `batch`, with cycle walking back into range - a bijection for every batch
+// size, evaluable per index, so kernels can gather through it without materialising the index buffer.
+struct PermFn {
+    int inline_on;          // 1: evaluate perm_index() in the consuming kernel (no perm buffer)
+    int half_bits;
+    int64_t batch;
+    uint64_t seed, epoch;
+    const uint64_t* d_epoch;   // optional device scalar added to `epoch` (CUDA-graph replay)
+};
+__host__ inline int perm_half_bits(int64_t batch) {
+    int bits = 2;
+    while (bits < 32 && (1ll << bits) < batch) bits += 2;
+    return bits / 2;
+}
+__device__ inline void perm_keys(uint64_t seed, uint64_t epoch, uint32_t (&k)[4]) {
+    Philox::gen(seed, 0x7065726Du /* 'perm' */, 3u, (uint32_t)epoch, (uint32_t)(epoch >> 32), k);
+}
+__device__ inline uint32_t feistel(uint32_t x, int half_bits, const uint32_t (&k)[4]) {
+    const uint32_t hm = (1u << half_bits) - 1u;
+    uint32_t l = x >> half_bits, r = x & hm;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        uint32_t f = (r ^ k[i]) * 0x9E3779B1u;
+        f ^= f >> 15; f *= 0x85EBCA77u; f ^= f >> 13;
+        const uint32_t nl = r, nr = l ^ (f & hm);
+        l = nl; r = nr;
+    }
+    return (l << half_bits) | r;
+}
+__device__ inline int64_t perm_index(int64_t i, int64_t batch, int half_bits, const uint32_t (&k)[4]) {
+    uint32_t x = (uint32_t)i;
+    do { x = feistel(x, half_bits, k); } while ((int64_t)x >= batch);
+    return (int64_t)x;
+}
+
 static inline cudaStream_t as_stream(ppo_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
 }  // namespace ppo

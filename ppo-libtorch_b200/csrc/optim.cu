@@ -236,18 +236,6 @@ __global__ void __launch_bounds__(EV_THREADS) explained_variance_kernel(int64_t 
 // ------------------------------------------------------------------------------------------------
 // Permutation of [0, batch): a 4-round Feistel network on the smallest even-width bit domain that
 // covers `batch`, with cycle walking back into range (a bijection for every batch size).
-__device__ inline uint32_t feistel(uint32_t x, int half_bits, const uint32_t (&k)[4]) {
-    const uint32_t hm = (1u << half_bits) - 1u;
-    uint32_t l = x >> half_bits, r = x & hm;
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        uint32_t f = (r ^ k[i]) * 0x9E3779B1u;
-        f ^= f >> 15; f *= 0x85EBCA77u; f ^= f >> 13;
-        const uint32_t nl = r, nr = l ^ (f & hm);
-        l = nl; r = nr;
-    }
-    return (l << half_bits) | r;
-}
 __global__ void __launch_bounds__(256) permutation_kernel(int64_t batch, int half_bits, uint64_t seed, uint64_t epoch,
                                                           const uint64_t* __restrict__ d_epoch,
                                                           int32_t* __restrict__ out) {
@@ -255,10 +243,67 @@ __global__ void __launch_bounds__(256) permutation_kernel(int64_t batch, int hal
     if (i >= batch) return;
     if (d_epoch) epoch += *d_epoch;
     uint32_t r[4];
-    Philox::gen(seed, 0x7065726Du /* 'perm' */, 3u, (uint32_t)epoch, (uint32_t)(epoch >> 32), r);
-    uint32_t x = (uint32_t)i;
-    do { x = feistel(x, half_bits, r); } while ((int64_t)x >= batch);
-    out[i] = (int32_t)x;
+    perm_keys(seed, epoch, r);
+    out[i] = (int32_t)perm_index(i, batch, half_bits, r);
+}
+
+// adv_moments_kernel for ALL epochs of an update at once: the advantages are fixed during the update and the
+// permutation of epoch e is a function of (seed, e), so the E x MB minibatch statistics (and, under data parallelism,
+// their ONE allreduce) can be produced before the first optimiser step.  blockIdx.x = e * n_mb + mb; same slicing and
+// summation order as adv_moments_kernel => the same numbers as the per-epoch path.
+__global__ void __launch_bounds__(ADV_THREADS) adv_moments_all_kernel(const float* __restrict__ adv, int64_t batch,
+                                                                      int mb_size, int n_mb, int n_epochs, int half_bits,
+                                                                      uint64_t seed, uint64_t epoch0,
+                                                                      const uint64_t* __restrict__ d_epoch,
+                                                                      double* __restrict__ ws, float* __restrict__ stats_out,
+                                                                      double* __restrict__ partial_out) {
+    __shared__ double sh[ADV_THREADS / 32];
+    __shared__ bool last;
+    const int emb = blockIdx.x, e = emb / n_mb, mb = emb % n_mb, sl = blockIdx.y;
+    uint32_t key[4];
+    perm_keys(seed, epoch0 + (uint64_t)e + (d_epoch ? *d_epoch : 0ull), key);
+    const int64_t start = (int64_t)mb * mb_size;
+    int64_t cnt = batch - start;
+    if (cnt > mb_size) cnt = mb_size;
+    if (cnt < 0) cnt = 0;
+    const int64_t per = (cnt + ADV_SLICES - 1) / ADV_SLICES;
+    const int64_t i0 = sl * per, i1 = i0 + per < cnt ? i0 + per : cnt;
+    double s = 0.0, q = 0.0;
+    for (int64_t i = i0 + threadIdx.x; i < i1; i += ADV_THREADS) {
+        const double x = (double)__ldg(adv + perm_index(start + i, batch, half_bits, key));
+        s += x;
+        q += x * x;
+    }
+    s = block_sum<ADV_THREADS>(s, sh);
+    q = block_sum<ADV_THREADS>(q, sh);
+    const int n_all = n_epochs * n_mb;
+    unsigned int* tickets = reinterpret_cast<unsigned int*>(ws + (size_t)n_all * ADV_SLICES * 2);
+    if (threadIdx.x == 0) {
+        ws[((size_t)emb * ADV_SLICES + sl) * 2 + 0] = s;
+        ws[((size_t)emb * ADV_SLICES + sl) * 2 + 1] = q;
+        __threadfence();
+        last = (atomicAdd(tickets + emb, 1u) == ADV_SLICES - 1);
+    }
+    __syncthreads();
+    if (!last || threadIdx.x != 0) return;
+    __threadfence();
+    double S = 0.0, Q = 0.0;
+    for (int k = 0; k < ADV_SLICES; k++) {
+        S += ws[((size_t)emb * ADV_SLICES + k) * 2 + 0];
+        Q += ws[((size_t)emb * ADV_SLICES + k) * 2 + 1];
+    }
+    tickets[emb] = 0;
+    const double n = (double)cnt;
+    if (partial_out) {
+        partial_out[emb * 3 + 0] = n; partial_out[emb * 3 + 1] = S; partial_out[emb * 3 + 2] = Q;
+    }
+    if (stats_out) {
+        const double mean = cnt > 0 ? S / n : 0.0;
+        double var = (Q - n * mean * mean) / (n - 1.0);
+        if (var < 0.0) var = 0.0;
+        stats_out[emb * 2 + 0] = (float)mean;
+        stats_out[emb * 2 + 1] = (float)sqrt(var);
+    }
 }
 
 }  // namespace ppo
@@ -338,10 +383,23 @@ extern "C" int ppo_make_permutation(int64_t batch, uint64_t seed, uint64_t epoch
                                     int32_t* perm_out, ppo_stream_t stream) {
     PPO_REQUIRE(batch >= 0 && batch <= 0x7fffffffLL && (perm_out || batch == 0), "ppo_make_permutation: bad arguments");
     if (batch == 0) return PPO_OK;
-    int bits = 2;
-    while (bits < 32 && (1ll << bits) < batch) bits += 2;
     const int64_t blocks = (batch + 255) / 256;
-    permutation_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(batch, bits / 2, seed, epoch, d_epoch, perm_out);
+    permutation_kernel<<<(unsigned)blocks, 256, 0, as_stream(stream)>>>(batch, perm_half_bits(batch), seed, epoch, d_epoch,
+                                                                        perm_out);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
+extern "C" int ppo_adv_stats_all_epochs(const float* adv, int64_t batch, int mb_size, int n_mb, int n_epochs, uint64_t seed,
+                                        uint64_t epoch0, const uint64_t* d_epoch, float* stats_out, double* partial_out,
+                                        void* workspace, ppo_stream_t stream) {
+    PPO_REQUIRE(adv && workspace && mb_size >= 1 && n_mb >= 0 && n_epochs >= 0 && batch >= 0 && batch <= 0x7fffffffLL,
+                "ppo_adv_stats_all_epochs: bad arguments");
+    PPO_REQUIRE(stats_out || partial_out, "ppo_adv_stats_all_epochs: no output requested");
+    if (n_mb == 0 || n_epochs == 0) return PPO_OK;
+    adv_moments_all_kernel<<<dim3(n_mb * n_epochs, ADV_SLICES), ADV_THREADS, 0, as_stream(stream)>>>(
+        adv, batch, mb_size, n_mb, n_epochs, perm_half_bits(batch), seed, epoch0, d_epoch,
+        reinterpret_cast<double*>(workspace), stats_out, partial_out);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
 }

@@ -17,6 +17,10 @@
 #include "common.cuh"
 #include "update.cuh"
 
+extern "C" int ppo_adv_stats_all_epochs(const float* adv, int64_t batch, int mb_size, int n_mb, int n_epochs, uint64_t seed,
+                                        uint64_t epoch0, const uint64_t* d_epoch, float* stats_out, double* partial_out,
+                                        void* workspace, ppo_stream_t stream);
+
 namespace ppo {
 int clip_adamw_launch(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_params, float lr,
                       const float* d_lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
@@ -179,8 +183,8 @@ extern "C" ppo_trainer* ppo_trainer_create(const ppo_trainer_cfg* c) {
         {"ret", (void**)&t->ret, (size_t)T * N * 4},
         {"masks", (void**)&t->masks, masked ? (size_t)T * N * K : 0},
         {"perm", (void**)&t->perm, (size_t)t->B * 4},
-        {"adv_stats", (void**)&t->adv_stats, (size_t)t->n_mb * 2 * 4},
-        {"adv_partial", (void**)&t->adv_partial, (size_t)t->n_mb * 3 * 8},
+        {"adv_stats", (void**)&t->adv_stats, (size_t)t->n_mb * (c->update_epochs > 0 ? c->update_epochs : 1) * 2 * 4},
+        {"adv_partial", (void**)&t->adv_partial, (size_t)t->n_mb * (c->update_epochs > 0 ? c->update_epochs : 1) * 3 * 8},
         {"diag", (void**)&t->diag_hist, (size_t)(t->n_opt > 0 ? t->n_opt : 1) * 8 * 4},
         {"ev_out", (void**)&t->ev_out, 4},
         {"norm_out", (void**)&t->norm_out, 4},
@@ -188,7 +192,8 @@ extern "C" ppo_trainer* ppo_trainer_create(const ppo_trainer_cfg* c) {
         {"scalars", (void**)&t->d_scal, sizeof(Scalars)},
         {"upd_ws", (void**)&t->upd_ws, (size_t)ppo_update_workspace_bytes(&c->dims)},
         {"ev_ws", (void**)&t->ev_ws, (size_t)ppo_explained_variance_workspace_bytes()},
-        {"adv_ws", (void**)&t->adv_ws, (size_t)ppo_adv_stats_workspace_bytes(t->n_mb)},
+        {"adv_ws", (void**)&t->adv_ws,
+         (size_t)ppo_adv_stats_workspace_bytes(t->n_mb * (c->update_epochs > 0 ? c->update_epochs : 1))},
     };
     size_t total = 0;
     for (auto& it : items) total += al256(it.bytes);
@@ -352,12 +357,15 @@ static int phase_rollout(ppo_trainer* t, cudaStream_t st) {
                    c.gae_lambda, c.use_gae, t->adv, t->ret, st);
 }
 
+static uint64_t perm_seed(const ppo_trainer_cfg& c) {   // rank-salted: every rank permutes its own shard
+    return c.seed ^ (0xA5A5A5A5ull * (uint64_t)(c.rank + 1));
+}
+
 static int phase_begin_epoch(ppo_trainer* t, int epoch, cudaStream_t st) {
     const ppo_trainer_cfg& c = t->cfg;
     PhaseTimer pt(t, PH_EPOCH, st);
     // rank-salted seed: every rank permutes its own shard independently
-    int rc = ppo_make_permutation(t->B, c.seed ^ (0xA5A5A5A5ull * (uint64_t)(c.rank + 1)), (uint64_t)epoch,
-                                  &t->d_scal->epoch_counter, t->perm, st);
+    int rc = ppo_make_permutation(t->B, perm_seed(c), (uint64_t)epoch, &t->d_scal->epoch_counter, t->perm, st);
     if (rc) return rc;
     if (!c.hyper.norm_adv) return PPO_OK;
     if (c.world_size > 1 && t->comm) {
@@ -384,7 +392,21 @@ static int phase_minibatch_grads(ppo_trainer* t, int mb, cudaStream_t st) {
 }
 
 // single-GPU iterations: gradient + reduction + clip + AdamW back to back, the optimiser fused into the reduction launch
-static int phase_minibatch_step(ppo_trainer* t, int mb, cudaStream_t st) {
+// whole-iteration path: the E x MB minibatch statistics in one launch (+ one allreduce under data parallelism)
+static int phase_all_epoch_stats(ppo_trainer* t, cudaStream_t st) {
+    const ppo_trainer_cfg& c = t->cfg;
+    if (!c.hyper.norm_adv || c.update_epochs == 0) return PPO_OK;
+    const int n_all = t->n_mb * c.update_epochs;
+    const bool dp = c.world_size > 1 && t->comm;
+    int rc = ppo_adv_stats_all_epochs(t->adv, t->B, t->mb_size, t->n_mb, c.update_epochs, perm_seed(c), 0,
+                                      &t->d_scal->epoch_counter, dp ? nullptr : t->adv_stats, dp ? t->adv_partial : nullptr,
+                                      t->adv_ws, st);
+    if (rc || !dp) return rc;
+    if ((rc = ppo_comm_allreduce_f64(t->comm, t->adv_partial, (int64_t)n_all * 3, st))) return rc;
+    return ppo_adv_stats_finalize(t->adv_partial, n_all, t->adv_stats, st);
+}
+
+static int phase_minibatch_step(ppo_trainer* t, int epoch, int mb, cudaStream_t st) {
     const ppo_trainer_cfg& c = t->cfg;
     const int64_t start = (int64_t)mb * t->mb_size;
     int64_t cnt = t->B - start;
@@ -398,10 +420,13 @@ static int phase_minibatch_step(ppo_trainer* t, int mb, cudaStream_t st) {
     f.step_host = (int64_t)k + 1; f.d_step = &t->d_scal->step_base; f.max_grad_norm = c.max_grad_norm;
     f.norm_out = t->norm_out; f.diag_hist = t->diag_hist + (size_t)k * 8;
     const bool peer = c.world_size > 1;   // caller checked peer_ready
+    ppo::PermFn pf{};
+    pf.inline_on = 1; pf.half_bits = ppo::perm_half_bits(t->B); pf.batch = t->B; pf.seed = perm_seed(c);
+    pf.epoch = (uint64_t)epoch; pf.d_epoch = &t->d_scal->epoch_counter;
     return ppo::update_minibatch_fused(t->params, &c.dims, t->obs, t->masks, t->actions, t->logprobs, t->adv, t->ret,
-                                       t->values, t->perm, start, (int)cnt, 1.0f / ((float)cnt * (float)c.world_size),
-                                       t->adv_stats + 2 * mb, &c.hyper, t->upd_ws, t->grads, t->grads + t->P, &f, st,
-                                       peer ? &t->peer : nullptr);
+                                       t->values, nullptr, start, (int)cnt, 1.0f / ((float)cnt * (float)c.world_size),
+                                       t->adv_stats + 2 * ((size_t)epoch * t->n_mb + mb), &c.hyper, t->upd_ws, t->grads,
+                                       t->grads + t->P, &f, st, peer ? &t->peer : nullptr, &pf);
 }
 
 static int phase_apply(ppo_trainer* t, cudaStream_t st) {
@@ -435,15 +460,18 @@ static int enqueue_iteration(ppo_trainer* t, cudaStream_t st) {
     int rc;
     t->opt_in_iter = 0;
     if ((rc = phase_rollout(t, st))) return rc;
+    const bool dp = t->cfg.world_size > 1 && t->comm;
+    const bool fused = (!dp || t->peer_ready) && !t->profile;
+    if (fused) {   // no per-epoch launches: statistics of every epoch up front, permutation evaluated inside the update kernel
+        if ((rc = phase_all_epoch_stats(t, st))) return rc;
+        for (int e = 0; e < t->cfg.update_epochs; e++)
+            for (int mb = 0; mb < t->n_mb; mb++)
+                if ((rc = phase_minibatch_step(t, e, mb, st))) return rc;
+        return phase_tail(t, st);
+    }
     for (int e = 0; e < t->cfg.update_epochs; e++) {
         if ((rc = phase_begin_epoch(t, e, st))) return rc;
-        const bool dp = t->cfg.world_size > 1 && t->comm;
-        const bool fused = (!dp || t->peer_ready) && !t->profile;
         for (int mb = 0; mb < t->n_mb; mb++) {
-            if (fused) {
-                if ((rc = phase_minibatch_step(t, mb, st))) return rc;
-                continue;
-            }
             if ((rc = phase_minibatch_grads(t, mb, st))) return rc;
             if ((rc = phase_apply(t, st))) return rc;
         }

@@ -48,13 +48,19 @@ __global__ void __launch_bounds__(MLP_THREADS) update_kernel(const UpdArgs a) {
 
     const int ntiles = (a.mb_size + TM - 1) / TM;
     const int t = threadIdx.x;
+    uint32_t pkey[4] = {0u, 0u, 0u, 0u};
+    if (!a.perm && a.pf.inline_on) perm_keys(a.pf.seed, a.pf.epoch + (a.pf.d_epoch ? *a.pf.d_epoch : 0ull), pkey);
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int r0 = tile * TM;
         const int rows = min(TM, a.mb_size - r0);
         __syncthreads();
         if (t < TM) {
             int64_t idx = -1;
-            if (t < rows) idx = a.perm ? (int64_t)a.perm[a.mb_start + r0 + t] : a.mb_start + r0 + t;
+            if (t < rows) {
+                if (a.perm) idx = (int64_t)a.perm[a.mb_start + r0 + t];
+                else if (a.pf.inline_on) idx = perm_index(a.mb_start + r0 + t, a.pf.batch, a.pf.half_bits, pkey);
+                else idx = a.mb_start + r0 + t;
+            }
             sidx[t] = idx;
         }
         __syncthreads();
@@ -525,8 +531,10 @@ int ppo::update_minibatch_fused(const float* params, const ppo_dims* dims, const
                                 const int32_t* actions, const float* old_logprob, const float* adv, const float* ret,
                                 const float* old_val, const int32_t* perm, int64_t mb_start, int mb_size, float inv_n,
                                 const float* adv_stats, const ppo_hyper* h_hyper, void* workspace, float* grads_out,
-                                float* diag_out, const FuseAdam* fuse, cudaStream_t st, const PeerArgs* peer) {
+                                float* diag_out, const FuseAdam* fuse, cudaStream_t st, const PeerArgs* peer,
+                                const PermFn* pf) {
     UpdArgs a{};
+    if (pf) a.pf = *pf;
     if (peer) {
         Dims dd;
         if (int rc = make_dims(dims, &dd)) return rc;

@@ -21,6 +21,7 @@ struct UpdArgs {
     const float* ret;
     const float* old_val;
     const int32_t* perm;
+    PermFn pf;       // perm == nullptr && pf.inline_on: rows are perm_index(mb_start + i) evaluated in the kernel
     int64_t mb_start;
     int mb_size;
     float inv_n;
@@ -67,7 +68,8 @@ int update_minibatch_fused(const float* params, const ppo_dims* dims, const floa
                            const int32_t* actions, const float* old_logprob, const float* adv, const float* ret,
                            const float* old_val, const int32_t* perm, int64_t mb_start, int mb_size, float inv_n,
                            const float* adv_stats, const ppo_hyper* h_hyper, void* workspace, float* grads_out,
-                           float* diag_out, const FuseAdam* fuse, cudaStream_t st, const PeerArgs* peer = nullptr);
+                           float* diag_out, const FuseAdam* fuse, cudaStream_t st, const PeerArgs* peer = nullptr,
+                           const PermFn* pf = nullptr);
 
 // update_tc.cu: returns PPO_ERR_UNSUPPORTED (without touching the error string) when the shape is outside the
 // tensor-core kernel's envelope (hidden != 64, obs_dim > 7, sumK > 32), PPO_OK after launching, else an error.

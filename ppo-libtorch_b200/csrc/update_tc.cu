@@ -416,6 +416,8 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
             int act0;        // action of head 0 (single-head fast path)
             bool on;
         };
+        uint32_t pkey[4] = {0u, 0u, 0u, 0u};
+        if (!a.perm && a.pf.inline_on) perm_keys(a.pf.seed, a.pf.epoch + (a.pf.d_epoch ? *a.pf.d_epoch : 0ull), pkey);
         auto gather = [&](int tile) {
             RowIn in;
             const int rloc = tile * TC_ROWS + wt;
@@ -425,7 +427,9 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
             in.old_logp = in.adv = in.ret = in.old_val = 0.0f;
             in.act0 = 0;
             if (in.on) {
-                const int64_t r = a.perm ? (int64_t)__ldg(a.perm + a.mb_start + rloc) : a.mb_start + rloc;
+                const int64_t r = a.perm ? (int64_t)__ldg(a.perm + a.mb_start + rloc)
+                                         : (a.pf.inline_on ? perm_index(a.mb_start + rloc, a.pf.batch, a.pf.half_bits, pkey)
+                                                           : a.mb_start + rloc);
                 in.r = r;
                 if (O == 4) {
                     const float4 o4 = __ldg(reinterpret_cast<const float4*>(a.obs + r * 4));
