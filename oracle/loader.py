@@ -221,6 +221,10 @@ class Reference:
         L.ref_trainer_get_params.argtypes = [C.c_void_p, _f32p]
         L.ref_trainer_set_params.argtypes = [C.c_void_p, _f32p]
         L.ref_trainer_get_grads.argtypes = [C.c_void_p, _f32p]
+        if hasattr(L, "ref_trainer_save"):
+            L.ref_trainer_save.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+            L.ref_trainer_load.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+            L.ref_trainer_opt_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]
         L.ref_agent_forward.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _f32p, _f32p]
         L.ref_agent_evaluate.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, C.c_void_p, _i64p, C.c_int,
                                          _f32p, _f32p, _f32p]
@@ -306,6 +310,23 @@ class RefTrainer:
         if self.h:
             self.L.ref_trainer_destroy(self.h)
             self.h = None
+
+    def save(self, agent_file=None, optimizer_file=None):
+        """torch::save of the reference's Agent / AdamW (PPO/PPO_Discrete.cpp:670-672)"""
+        self.ref._ck(self.L.ref_trainer_save(C.c_void_p(self.h), agent_file.encode() if agent_file else None,
+                                             optimizer_file.encode() if optimizer_file else None))
+
+    def load(self, agent_file=None, optimizer_file=None):
+        """torch::load into the reference's Agent / AdamW (PPO/PPO_Discrete.cpp:813, :832)"""
+        self.ref._ck(self.L.ref_trainer_load(C.c_void_p(self.h), agent_file.encode() if agent_file else None,
+                                             optimizer_file.encode() if optimizer_file else None))
+
+    def opt_state(self, index, numel):
+        step = C.c_int64()
+        m, v = np.zeros(numel, np.float32), np.zeros(numel, np.float32)
+        self.ref._ck(self.L.ref_trainer_opt_state(C.c_void_p(self.h), index, C.byref(step),
+                                                  m.ctypes.data_as(C.c_void_p), v.ctypes.data_as(C.c_void_p)))
+        return step.value, m, v
 
     def set_nvec(self, nvec):
         nv = np.ascontiguousarray(nvec, np.int64)

@@ -162,6 +162,42 @@ void* ref_trainer_create(int64_t obs_size, int64_t action_size, float lr, int64_
 
 void ref_trainer_destroy(void* h) { delete static_cast<RefTrainer*>(h); }
 
+// The reference's checkpoint calls on the reference's own Agent class and AdamW:
+// torch::save(m_agent, ...) / torch::save(*m_optimizer, ...) (PPO/PPO_Discrete.cpp:670-672) and
+// torch::load(m_agent, ...) / torch::load(*m_optimizer, ...) (:813, :832).  (The reference BINARY cannot be used for
+// this on Linux: loadPolicyFromCheckpoint compares last_write_time against a default-constructed file_time_type, which
+// is the year-2174 epoch of libstdc++'s file_clock, so it never finds a newest file and throws on the empty name.)
+int ref_trainer_save(void* h, const char* agent_file, const char* optimizer_file) {
+    auto* t = static_cast<RefTrainer*>(h);
+    try {
+        if (agent_file) torch::save(t->agent, agent_file);
+        if (optimizer_file) torch::save(*t->opt, optimizer_file);
+        return 0;
+    } catch (const std::exception& e) { return fail(e); }
+}
+int ref_trainer_load(void* h, const char* agent_file, const char* optimizer_file) {
+    auto* t = static_cast<RefTrainer*>(h);
+    try {
+        if (agent_file) torch::load(t->agent, agent_file);
+        if (optimizer_file) torch::load(*t->opt, optimizer_file);
+        return 0;
+    } catch (const std::exception& e) { return fail(e); }
+}
+// AdamW state of parameter `index` after a load / step: step count and the two moment tensors (flat)
+int ref_trainer_opt_state(void* h, int index, int64_t* step, float* exp_avg, float* exp_avg_sq) {
+    auto* t = static_cast<RefTrainer*>(h);
+    try {
+        auto& p = t->opt->param_groups()[0].params()[index];
+        auto it = t->opt->state().find(p.unsafeGetTensorImpl());
+        if (it == t->opt->state().end()) { *step = -1; return 0; }
+        auto& st = static_cast<torch::optim::AdamWParamState&>(*it->second);
+        *step = st.step();
+        if (exp_avg) copy_out(st.exp_avg(), exp_avg);
+        if (exp_avg_sq) copy_out(st.exp_avg_sq(), exp_avg_sq);
+        return 0;
+    } catch (const std::exception& e) { return fail(e); }
+}
+
 // Multi-head nvec for getActionAndValueMasked (PPO/Agent.cpp:21 keeps a single head; the
 // member is public, the forward at :137-170 is generic over it).  Sum must equal action_size.
 int ref_trainer_set_nvec(void* h, const int64_t* nvec, int heads) {
