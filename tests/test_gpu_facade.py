@@ -144,3 +144,22 @@ def test_checkpoints_exchange_with_the_reference_classes(exe, tmp_path):
     assert np.array_equal(got, ref_params)                 # device slab <- reference archive -> our archive, bit for bit
     out = run(exe, str(b), 5 * BATCH, True)                # and training continues from it (optimizer state included)
     assert out.count("|    iterations") == 2 and "Exception" not in out
+
+
+def test_multidiscrete_driver_mountaincar(exe, tmp_path):
+    """PPO_MultiDiscrete (PPO/PPO_MultiDiscrete.cpp): MountainCar, CategoricalMasked head of 3 logits with the env's
+    all-valid mask, default max_episode_steps 200; the masked entropy is the correct formula (~ln 3 for the near-uniform
+    initial policy, CategoricalMasked.cpp:140-142) - unlike PPO_Discrete's clamped one."""
+    toml = TOML.format(total=3 * BATCH, cuda="true").replace("obs_size = 4", "obs_size = 2").replace(
+        "action_size = 2", "action_size = 3").replace("max_episode_steps = 500\n", "")
+    with open(tmp_path / "PPOConfig.toml", "w") as f:
+        f.write(toml)
+    p = subprocess.run([exe, "multidiscrete"], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-2000:]
+    m = re.findall(r"\|    entropy_loss         \| ([-0-9.]+)", p.stdout)
+    assert len(m) == 2 and all(1.0 < float(x) < 1.0987 for x in m), m
+    # 64 envs x 32 steps x 3 updates = 96 steps per env < 200: no episode can have finished yet -> no rollout/ block
+    assert "ep_len_mean" not in p.stdout
+    mod = torch.jit.load(str(tmp_path / "Models" / f"PPO_Agent_{3 * BATCH}_steps.pt"), map_location="cpu")
+    shapes = {k: tuple(v.shape) for k, v in mod.named_parameters()}
+    assert shapes["m_Actor.actorOutputLayer.weight"] == (3, 64) and shapes["m_Critic.criticInputLayer.weight"] == (64, 2)
