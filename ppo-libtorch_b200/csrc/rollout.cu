@@ -6,29 +6,9 @@
 // The policy is frozen during a rollout and envs are independent, so a CTA owns a tile of TM envs
 // for all T steps: env state, episode counters and the done flag stay in registers; the tile's
 // observations feed the shared-memory MLP directly; nothing but the [T,N,...] rollout rows touches HBM.
-#include "env.cuh"
-#include "policy.cuh"
+#include "rollout.cuh"
 
 namespace ppo {
-
-struct RollArgs {
-    const float* params;
-    Dims d;
-    ppo_rollout_cfg cfg;
-    float* state;
-    int32_t* ep_len;
-    float* ep_ret;
-    float* next_done;
-    float* next_value;
-    float* obs_buf;
-    int32_t* actions_buf;
-    float* logprobs_buf;
-    float* rewards_buf;
-    float* dones_buf;
-    float* values_buf;
-    uint8_t* mask_buf;
-    double* ep_stats;
-};
 
 template <class Env, int TM, int H>
 __global__ void __launch_bounds__(MLP_THREADS) rollout_kernel(const RollArgs a) {
@@ -465,10 +445,14 @@ static int launch_rollout64(const RollArgs& a, cudaStream_t st) {
 }
 
 static int g_rollout_impl = 1;   // 0 = generic kernel for every shape (ppo_debug_rollout_impl)
+static int g_rollout_tc_min = 8192;   // below ~8k envs a step is latency-bound and the FMA tiles (16 envs per CTA) win
 
 template <class Env>
 static int dispatch_rollout(const RollArgs& a, cudaStream_t st) {
     PPO_REQUIRE(a.d.O == Env::OBS, "rollout: obs_dim=%d but the env observes %d floats", a.d.O, Env::OBS);
+    // 128-env tensor-core tiles once there are enough envs to fill them (ppo_debug_rollout_impl: 2 = never, 3 = always)
+    if (rollout_tc_supported(a.d) && (g_rollout_impl == 3 || (g_rollout_impl == 1 && a.cfg.n_envs >= g_rollout_tc_min)))
+        return launch_rollout_tc<Env>(a, st);
     if (a.d.H == 64 && g_rollout_impl) {
         // small env counts: 16-env tiles so that two CTAs per SM overlap each other's serial env / sampling phase
         const int sms = sm_count() > 0 ? sm_count() : 148;

@@ -446,13 +446,19 @@ def test_permutation_is_bijection(P, batch):
                                                       # ragged last tile, multi-head
                                                       (0, 4, [2], False, 64, 4999, 6),
                                                       (1, 2, [3, 2], False, 64, 45, 12)])
-def test_fused_rollout_vs_oracle(P, orc, kind, O, nvec, masked, H, n, T):
-    """Every step of the fused rollout is checked from the GPU's own previous observation (single-step
+@pytest.mark.parametrize("impl", [1, 3])
+def test_fused_rollout_vs_oracle(P, orc, request, kind, O, nvec, masked, H, n, T, impl):
+    """impl 1 = the kernel the dispatcher picks (FMA tiles below 8192 envs), 3 = tensor-core tiles forced.
+    Every step of the fused rollout is checked from the GPU's own previous observation (single-step
     comparisons, so CartPole's chaos cannot amplify ulp differences): forward -> sample on the same Philox
     uniform -> env transition with truncation/auto-reset -> stored rollout rows; then bootstrap + GAE."""
     from philox_np import reset_uniforms, sample_uniforms
     seed, counter, base, max_ep = 4242, 1000, 64, 5
     K, heads = sum(nvec), len(nvec)
+    if impl == 3 and H != 64:
+        pytest.skip("tensor-core rollout tiles are hidden = 64 only")
+    P.capi.load().ppo_debug_rollout_impl(impl)
+    request.addfinalizer(lambda: P.capi.load().ppo_debug_rollout_impl(1))
     params = P.orthogonal_init_params(O, H, nvec, seed=11)
     params[-K:] = np.linspace(-0.3, 0.3, K)                      # non-uniform policy
     u0 = np.random.default_rng(1).uniform(size=(n, 4)).astype(np.float32)

@@ -7,7 +7,7 @@ import ppo_libtorch_b200 as P
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 T = int(sys.argv[2]) if len(sys.argv) > 2 else 128
 lib = P.capi.load()
-for impl in (0, 1):
+for impl in (0, 2, 3):   # generic FMA tiles, hidden-64 register-resident FMA tiles, tensor-core tiles
     lib.ppo_debug_rollout_impl(impl)
     tr = P.Trainer(num_envs=n, num_steps=T, nvec=(2,), seed=2)
     for _ in range(3):
@@ -23,7 +23,7 @@ for impl in (0, 1):
     print(f"impl={impl} n={n} T={T}: {ms:.3f} ms per rollout+GAE, {n * T / ms / 1e3:.1f} M env-steps/s")
     tr.close()
 
-lib.ppo_debug_rollout_impl(1)
+lib.ppo_debug_rollout_impl(2)
 ts = torch.zeros(8, dtype=torch.int64, device="cuda")
 import ctypes as C
 lib.ppo_debug_rollout_timeline(C.c_void_p(ts.data_ptr()))
