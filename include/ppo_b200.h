@@ -174,6 +174,14 @@ int64_t ppo_adv_stats_workspace_bytes(int n_mb);
 int ppo_adv_stats(const float* adv, const int32_t* perm, int64_t batch, int mb_size, int n_mb,
                   float* stats_out, double* partial_out, void* workspace, ppo_stream_t stream);
 int ppo_adv_stats_finalize(const double* partial, int n_mb, float* stats_out, ppo_stream_t stream);
+/* Packed rollout rows for the minibatch gather (no reference counterpart: the reference indexes six tensors with
+ * mbInds, PPO/PPO_Discrete.cpp:577-594).  rec_out [batch][16] floats, 64-byte aligned:
+ *   {obs[0..4) zero padded} {old_logprob, adv, ret, old_val} {action bits, 0, 0, 0} {0, 0, 0, 0}
+ * A permuted row then costs ONE aligned 64-byte DRAM burst instead of six scattered 32-byte sectors (measured at
+ * 16.8 M rows: 635 B of DRAM traffic per row before, profiles/r01j).  Single action head, obs_dim <= 4; old_val may
+ * be NULL (zeros). */
+int ppo_pack_rows(int64_t batch, int obs_dim, const float* obs, const int32_t* actions, const float* old_logprob,
+                  const float* adv, const float* ret, const float* old_val, float* rec_out, ppo_stream_t stream);
 /* The same statistics for all n_epochs x n_mb minibatches of one PPO update in ONE launch (the advantages are fixed
  * during the update, PPO/PPO_Discrete.cpp:567-594, and the permutation of epoch e is ppo_make_permutation(batch, seed,
  * epoch0 + e [+ *d_epoch]) evaluated inline, no index buffer).  stats_out [n_epochs*n_mb, 2] and / or partial_out
@@ -327,6 +335,9 @@ int ppo_debug_umma_probe(int mode, int fmt, const float* A, const float* B, floa
 /* Rollout kernel choice for hidden = 64: 1 (default) = register-resident-weights kernel, 0 = the generic tiled kernel
  * (what every other hidden width uses).  For A/B tests and benchmarks; no reference counterpart. */
 int ppo_debug_rollout_impl(int impl);
+/* 1 (default): trainers whose shape allows it (single head, unmasked, obs_dim <= 4) repack the rollout rows with
+ * ppo_pack_rows once per iteration and the update kernel gathers records; 0: gather from the six row arrays. */
+int ppo_debug_pack_rows(int on);
 /* d_ts = device buffer of 8 int64 (NULL switches it off): CTA 0 / thread 0 of the hidden = 64 rollout kernel stamps the
  * SM clock at the six phase edges of rollout step 2 (tools/rollout_bench.py prints the deltas). */
 int ppo_debug_rollout_timeline(long long* d_ts);

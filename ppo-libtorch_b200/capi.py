@@ -78,6 +78,8 @@ _PROTOS = {
     "ppo_trainer_peer_handle": (C.c_int, [C.c_void_p, C.c_char_p]),
     "ppo_trainer_set_peers": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "ppo_debug_rollout_impl": (C.c_int, [C.c_int]),
+    "ppo_debug_pack_rows": (C.c_int, [C.c_int]),
+    "ppo_pack_rows": (C.c_int, [C.c_int64, C.c_int] + [C.c_void_p] * 8),
     "ppo_debug_rollout_timeline": (C.c_int, [C.c_void_p]),
     "ppo_device_count": (C.c_int, []),
     "ppo_device_info": (C.c_int, [C.POINTER(C.c_int)] * 3),

@@ -390,6 +390,46 @@ extern "C" int ppo_make_permutation(int64_t batch, uint64_t seed, uint64_t epoch
     return PPO_OK;
 }
 
+// One 64-byte record per rollout row for the update kernel's gather (see ppo_pack_rows in the header)
+__global__ void pack_rows_kernel(int64_t batch, int O, const float* __restrict__ obs, const int32_t* __restrict__ actions,
+                                 const float* __restrict__ logp, const float* __restrict__ adv,
+                                 const float* __restrict__ ret, const float* __restrict__ val, float4* __restrict__ rec) {
+    // thread = (row, quarter): the four float4 of a record are written by four adjacent lanes (coalesced 64 B)
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = i >> 2;
+    const int q = (int)(i & 3);
+    if (r >= batch) return;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (q == 0) {
+        if (O == 4) v = __ldg(reinterpret_cast<const float4*>(obs) + r);
+        else {
+            float o[4] = {0.f, 0.f, 0.f, 0.f};
+            for (int k = 0; k < O; k++) o[k] = __ldg(obs + r * O + k);
+            v = make_float4(o[0], o[1], o[2], o[3]);
+        }
+    } else if (q == 1) {
+        v = make_float4(__ldg(logp + r), __ldg(adv + r), __ldg(ret + r), val ? __ldg(val + r) : 0.0f);
+    } else if (q == 2) {
+        v.x = __int_as_float(__ldg(actions + r));
+    }
+    rec[i] = v;
+}
+
+extern "C" int ppo_pack_rows(int64_t batch, int obs_dim, const float* obs, const int32_t* actions, const float* old_logprob,
+                             const float* adv, const float* ret, const float* old_val, float* rec_out,
+                             ppo_stream_t stream) {
+    PPO_REQUIRE(batch >= 0 && obs_dim >= 1 && obs_dim <= 4, "ppo_pack_rows: batch=%lld obs_dim=%d (1..4)", (long long)batch,
+                obs_dim);
+    if (batch == 0) return PPO_OK;
+    PPO_REQUIRE(obs && actions && old_logprob && adv && ret && rec_out, "ppo_pack_rows: null buffer");
+    PPO_REQUIRE((reinterpret_cast<uintptr_t>(rec_out) & 63) == 0, "ppo_pack_rows: rec_out must be 64-byte aligned");
+    const int64_t n = batch * 4;
+    pack_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(
+        batch, obs_dim, obs, actions, old_logprob, adv, ret, old_val, reinterpret_cast<float4*>(rec_out));
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
 extern "C" int ppo_adv_stats_all_epochs(const float* adv, int64_t batch, int mb_size, int n_mb, int n_epochs, uint64_t seed,
                                         uint64_t epoch0, const uint64_t* d_epoch, float* stats_out, double* partial_out,
                                         void* workspace, ppo_stream_t stream) {

@@ -68,6 +68,8 @@ struct ppo_trainer {
     float *adv_stats, *diag_hist, *ev_out, *norm_out;
     double *adv_partial, *ep_stats;
     void *upd_ws, *ev_ws, *adv_ws;
+    bool use_rec = false;
+    float* rec = nullptr;   // packed rollout rows [B][16] (ppo_pack_rows) or nullptr when the shape has no packed form
     Scalars* d_scal;
     // host
     float* h_diag = nullptr;    // pinned [n_opt, 8]
@@ -194,6 +196,7 @@ extern "C" ppo_trainer* ppo_trainer_create(const ppo_trainer_cfg* c) {
         {"ev_ws", (void**)&t->ev_ws, (size_t)ppo_explained_variance_workspace_bytes()},
         {"adv_ws", (void**)&t->adv_ws,
          (size_t)ppo_adv_stats_workspace_bytes(t->n_mb * (c->update_epochs > 0 ? c->update_epochs : 1))},
+        {"rec", (void**)&t->rec, (heads == 1 && !masked && O <= 4 && t->d.H == 64) ? (size_t)t->B * 64 : 0},
     };
     size_t total = 0;
     for (auto& it : items) total += al256(it.bytes);
@@ -336,6 +339,12 @@ static int push_scalars(ppo_trainer* t, float lr, cudaStream_t st) {
     return PPO_OK;
 }
 
+static int g_pack_rows = 1;   // ppo_debug_pack_rows
+extern "C" int ppo_debug_pack_rows(int on) {
+    g_pack_rows = on;
+    return PPO_OK;
+}
+
 static int phase_rollout(ppo_trainer* t, cudaStream_t st) {
     const ppo_trainer_cfg& c = t->cfg;
     PPO_CUDA(cudaMemsetAsync(t->ep_stats, 0, 3 * 8, st));
@@ -426,7 +435,8 @@ static int phase_minibatch_step(ppo_trainer* t, int epoch, int mb, cudaStream_t 
     return ppo::update_minibatch_fused(t->params, &c.dims, t->obs, t->masks, t->actions, t->logprobs, t->adv, t->ret,
                                        t->values, nullptr, start, (int)cnt, 1.0f / ((float)cnt * (float)c.world_size),
                                        t->adv_stats + 2 * ((size_t)epoch * t->n_mb + mb), &c.hyper, t->upd_ws, t->grads,
-                                       t->grads + t->P, &f, st, peer ? &t->peer : nullptr, &pf);
+                                       t->grads + t->P, &f, st, peer ? &t->peer : nullptr, &pf,
+                                       t->use_rec ? t->rec : nullptr);
 }
 
 static int phase_apply(ppo_trainer* t, cudaStream_t st) {
@@ -464,6 +474,13 @@ static int enqueue_iteration(ppo_trainer* t, cudaStream_t st) {
     const bool fused = (!dp || t->peer_ready) && !t->profile;
     if (fused) {   // no per-epoch launches: statistics of every epoch up front, permutation evaluated inside the update kernel
         if ((rc = phase_all_epoch_stats(t, st))) return rc;
+        const bool packed = t->rec && g_pack_rows && t->cfg.update_epochs > 0;
+        if (packed) {
+            PhaseTimer pt(t, PH_EPOCH, st);
+            if ((rc = ppo_pack_rows(t->B, t->d.O, t->obs, t->actions, t->logprobs, t->adv, t->ret, t->values, t->rec, st)))
+                return rc;
+        }
+        t->use_rec = packed;
         for (int e = 0; e < t->cfg.update_epochs; e++)
             for (int mb = 0; mb < t->n_mb; mb++)
                 if ((rc = phase_minibatch_step(t, e, mb, st))) return rc;

@@ -532,9 +532,10 @@ int ppo::update_minibatch_fused(const float* params, const ppo_dims* dims, const
                                 const float* old_val, const int32_t* perm, int64_t mb_start, int mb_size, float inv_n,
                                 const float* adv_stats, const ppo_hyper* h_hyper, void* workspace, float* grads_out,
                                 float* diag_out, const FuseAdam* fuse, cudaStream_t st, const PeerArgs* peer,
-                                const PermFn* pf) {
+                                const PermFn* pf, const float* rec) {
     UpdArgs a{};
     if (pf) a.pf = *pf;
+    a.rec = reinterpret_cast<const float4*>(rec);
     if (peer) {
         Dims dd;
         if (int rc = make_dims(dims, &dd)) return rc;
@@ -551,6 +552,7 @@ int ppo::update_minibatch_fused(const float* params, const ppo_dims* dims, const
     a.params = params; a.obs = obs; a.mask = mask; a.actions = actions; a.old_logprob = old_logprob;
     a.adv = adv; a.ret = ret; a.old_val = old_val; a.perm = perm; a.mb_start = mb_start; a.mb_size = mb_size;
     a.inv_n = inv_n; a.adv_stats = adv_stats; a.hp = *h_hyper;
+    if (a.rec) PPO_REQUIRE(a.d.heads == 1 && !mask && a.d.O <= 4, "packed rows: single head, no mask, obs_dim <= 4");
     const int P = num_params(a.d.O, a.d.H, a.d.K);
     a.slabs = reinterpret_cast<float*>(workspace);
     a.dpart = reinterpret_cast<double*>(reinterpret_cast<char*>(workspace) +

@@ -21,6 +21,8 @@ struct UpdArgs {
     const float* ret;
     const float* old_val;
     const int32_t* perm;
+    const float4* rec;   // optional packed rows (ppo_pack_rows): 64 B per row = one aligned DRAM burst instead of six
+                         // scattered 4-byte gathers; single-head, unmasked, obs_dim <= 4 only
     PermFn pf;       // perm == nullptr && pf.inline_on: rows are perm_index(mb_start + i) evaluated in the kernel
     int64_t mb_start;
     int mb_size;
@@ -69,7 +71,7 @@ int update_minibatch_fused(const float* params, const ppo_dims* dims, const floa
                            const float* old_val, const int32_t* perm, int64_t mb_start, int mb_size, float inv_n,
                            const float* adv_stats, const ppo_hyper* h_hyper, void* workspace, float* grads_out,
                            float* diag_out, const FuseAdam* fuse, cudaStream_t st, const PeerArgs* peer = nullptr,
-                           const PermFn* pf = nullptr);
+                           const PermFn* pf = nullptr, const float* rec = nullptr);
 
 // update_tc.cu: returns PPO_ERR_UNSUPPORTED (without touching the error string) when the shape is outside the
 // tensor-core kernel's envelope (hidden != 64, obs_dim > 7, sumK > 32), PPO_OK after launching, else an error.

@@ -431,6 +431,13 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
                                          : (a.pf.inline_on ? perm_index(a.mb_start + rloc, a.pf.batch, a.pf.half_bits, pkey)
                                                            : a.mb_start + rloc);
                 in.r = r;
+                if (a.rec) {   // packed row: {obs[4]} {old_logp, adv, ret, old_val} {action, -, -, -} {-}
+                    const float4 q0 = __ldg(a.rec + r * 4), q1 = __ldg(a.rec + r * 4 + 1), q2 = __ldg(a.rec + r * 4 + 2);
+                    in.o[0] = q0.x; in.o[1] = q0.y; in.o[2] = q0.z; in.o[3] = q0.w;
+                    in.old_logp = q1.x; in.adv = q1.y; in.ret = q1.z; in.old_val = q1.w;
+                    in.act0 = __float_as_int(q2.x);
+                    return in;
+                }
                 if (O == 4) {
                     const float4 o4 = __ldg(reinterpret_cast<const float4*>(a.obs + r * 4));
                     in.o[0] = o4.x; in.o[1] = o4.y; in.o[2] = o4.z; in.o[3] = o4.w;

@@ -622,3 +622,44 @@ def test_trainer_fused_step_equals_split_phases(P, math_mode, mode):
             np.testing.assert_allclose(ra[key], rb[key], rtol=1e-5, atol=1e-7, err_msg=key)
     a.close()
     b.close()
+
+
+# ---------------------------------------------------------------------------------------------- packed rows
+@pytest.mark.parametrize("O,batch", [(4, 1), (4, 4099), (2, 1000)])
+def test_pack_rows_layout(P, O, batch):
+    """ppo_pack_rows: record r = {obs zero-padded to 4} {old_logprob, adv, ret, old_val} {action bits, 0, 0, 0} {0 x 4}."""
+    rng = np.random.default_rng(5)
+    obs = rng.standard_normal((batch, O)).astype(np.float32)
+    act = rng.integers(0, 7, size=batch).astype(np.int32)
+    f = [rng.standard_normal(batch).astype(np.float32) for _ in range(4)]
+    rec = torch.full((batch, 16), 7.0, device="cuda")
+    d = [dev(obs), dev(act)] + [dev(x) for x in f]
+    rc = P.capi.load().ppo_pack_rows(batch, O, *[x.data_ptr() for x in d], rec.data_ptr(), None)
+    assert rc == 0, P.capi.last_error()
+    torch.cuda.synchronize()
+    r = rec.cpu().numpy()
+    want = np.zeros((batch, 16), np.float32)
+    want[:, :O] = obs
+    for i in range(4):
+        want[:, 4 + i] = f[i]
+    want[:, 8] = act.view(np.float32)
+    assert np.array_equal(r.view(np.uint32), want.view(np.uint32))
+
+
+def test_trainer_packed_rows_bit_identical(P, request):
+    """The update kernel gathering 64-byte records (default) and gathering from the six row arrays read the same
+    numbers: two iterations leave bit-identical parameters and optimiser state."""
+    lib = P.capi.load()
+    request.addfinalizer(lambda: lib.ppo_debug_pack_rows(1))
+    out = []
+    for on in (1, 0):
+        lib.ppo_debug_pack_rows(on)
+        tr = P.Trainer(num_envs=1024, num_steps=64, num_minibatches=4, update_epochs=2, nvec=(2,), seed=5)
+        for _ in range(2):
+            res = tr.iterate(1e-3)
+        torch.cuda.synchronize()
+        out.append((tr.get_params().copy(), tr.get_opt_state(), res))
+        tr.close()
+    assert np.array_equal(out[0][0], out[1][0])
+    assert np.array_equal(out[0][1][0], out[1][1][0]) and np.array_equal(out[0][1][1], out[1][1][1])
+    assert out[0][2]["loss"] == out[1][2]["loss"]
