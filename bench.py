@@ -33,9 +33,9 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "cartpole_4096x128_h64"
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE update-kernel launch from an `ncu --set full` capture of this
-# command (profiles/r01h_update_tc_kernel_v5_ncu.txt): 18.69 MB + 16 KB.  Algorithmic bytes per launch are 131072 rows x
-# 36 B + the 0.5 MB permutation slice = 5.2 MB: the gather through the permutation pulls a 32 B sector per 4 B field.
-NCU_TRAFFIC = {("cartpole_4096x128_h64", 2): 18.69e6 + 16.1e3}
+# command (profiles/r01k_update_tc_ncu.txt, cold L2): 14.83 MB + 10 KB.  Algorithmic bytes per launch are 131072 rows x
+# 36 B = 4.7 MB, fetched as 64-byte packed records = 8.4 MB (ppo_pack_rows), + 37 KB of parameters per CTA.
+NCU_TRAFFIC = {("cartpole_4096x128_h64", 2): 14.83e6 + 10.5e3}
 HYPER = dict(gamma=0.98, gae_lambda=0.95, clip_coef=0.2, norm_adv=True, clip_vloss=True, ent_coef=0.0, vf_coef=0.5,
              max_grad_norm=0.5)
 LR0 = 1e-3
@@ -386,11 +386,12 @@ def run_b200(args, wl_name):
                 " (bf16 cuBLAS sustained)",
                 "flops_per_launch": flops_per_launch, "ms_per_launch": upd_ms_per,
                 "share_of_step": upd_ms / phase_total if phase_total else None}
-    # one GPU / peer-memory DP: scalars, rollout, gae, all-epoch advantage statistics, per minibatch {update,
+    # one GPU / peer-memory DP: scalars, rollout, gae, all-epoch advantage statistics, row packing, per minibatch {update,
     # reduce+clip+AdamW}, explained variance.  NCCL DP: per epoch {permutation, moments, finalize}, per minibatch
     # {update, reduce, clip_adamw} (NCCL's own kernels are not counted: not ours).
     if world == 1 or not args.no_peer:
-        launches = 4 + wl["E"] * wl["MB"] * 2 + 1 + (1 if world > 1 else 0)
+        packed = 1 if (wl["H"] == 64 and len(wl["nvec"]) == 1 and wl["O"] <= 4) else 0   # + ppo_pack_rows
+        launches = 4 + packed + wl["E"] * wl["MB"] * 2 + 1 + (1 if world > 1 else 0)
     else:
         launches = 3 + wl["E"] * (3 + wl["MB"] * 3) + 1
 
