@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PPO_B200_ABI_VERSION 2
+#define PPO_B200_ABI_VERSION 3
 #define PPO_MAX_HEADS 8
 #define PPO_MAX_LOGITS 64
 
@@ -155,12 +155,24 @@ typedef struct {
     uint64_t seed;
     uint64_t counter; /* advances by n_steps per rollout */
     const uint64_t* d_counter; /* optional DEVICE scalar added to `counter` (CUDA-graph replay) */
+    /* optional episode log [T,n] (both or neither): length / return of the episode that FINISHED at (t, env) - by
+     * termination or truncation, before the auto-reset - and 0 / 0 where none did: the values stepEnvs pushes into its
+     * CircularBuffer(100) (PPO/PPO_Discrete.cpp:453-458, 474-480), in the same (step, env) order. */
+    int32_t* fin_len;
+    float* fin_ret;
 } ppo_rollout_cfg;
 int ppo_rollout(const float* params, const ppo_dims* dims, const ppo_rollout_cfg* cfg,
                 float* state_soa, int32_t* ep_len, float* ep_ret, float* next_done,
                 float* next_value, float* obs_buf, int32_t* actions_buf, float* logprobs_buf, float* rewards_buf,
                 float* dones_buf, float* values_buf, float* adv_buf, float* ret_buf,
                 uint8_t* mask_buf, double* ep_stats, ppo_stream_t stream);
+
+/* The newest (at most max_n <= 1024) finished episodes of an episode log, oldest first: what the reference's
+ * CircularBuffer(max_n) holds after pushing the whole log (PPO/PPO_Discrete.cpp:474-480; Utils.h:30-79).  One CTA walks
+ * the log backwards from (T-1, n-1) until max_n episodes are found.  out_count: device int32; out_len / out_ret:
+ * device [max_n] (entries past *out_count are untouched). */
+int ppo_episode_tail(const int32_t* fin_len, const float* fin_ret, int64_t rows, int max_n, int32_t* out_count,
+                     int32_t* out_len, float* out_ret, ppo_stream_t stream);
 
 /* ---- K5: fused minibatch forward + PPO loss + backward ----------------------------------- */
 /* PPO/PPO_Discrete.cpp:591-594: per-minibatch advantage mean / unbiased std for the n_mb
@@ -270,6 +282,12 @@ int ppo_trainer_set_params(ppo_trainer* t, const float* h_params);
 int ppo_trainer_get_params(ppo_trainer* t, float* h_params);
 /* optimizer state for checkpointing: exp_avg, exp_avg_sq, step */
 int ppo_trainer_get_opt_state(ppo_trainer* t, float* h_exp_avg, float* h_exp_avg_sq, int64_t* h_step);
+/* After a synchronised ppo_trainer_iterate(want_result) / ppo_trainer_finish: the newest finished episodes of that
+ * iteration, oldest first, at most min(max_n, PPO_EPISODE_TAIL) of them -> host arrays; returns how many.  Pushing them
+ * into a CircularBuffer(100) reproduces the reference's ring (PPO/PPO_Discrete.cpp:474-480) exactly: the ring only ever
+ * holds the last 100 episodes, so older ones of the same iteration could not have survived. */
+#define PPO_EPISODE_TAIL 100
+int ppo_trainer_last_episodes(ppo_trainer* t, int max_n, int32_t* h_len, float* h_ret);
 int ppo_trainer_set_opt_state(ppo_trainer* t, const float* h_exp_avg, const float* h_exp_avg_sq, int64_t step);
 /* initEnvs (PPO_Discrete.cpp:365-402) */
 int ppo_trainer_reset_envs(ppo_trainer* t);

@@ -43,7 +43,7 @@ class RolloutCfg(C.Structure):
                 ("max_episode_steps", C.c_int32), ("gamma", C.c_float), ("gae_lambda", C.c_float),
                 ("use_gae", C.c_int32), ("entropy_mode", C.c_int32), ("masked", C.c_int32),
                 ("env_id_base", C.c_uint32), ("seed", C.c_uint64), ("counter", C.c_uint64),
-                ("d_counter", C.c_void_p)]
+                ("d_counter", C.c_void_p), ("fin_len", C.c_void_p), ("fin_ret", C.c_void_p)]
 
 
 class TrainerCfg(C.Structure):
@@ -79,6 +79,8 @@ _PROTOS = {
     "ppo_trainer_set_peers": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "ppo_debug_rollout_impl": (C.c_int, [C.c_int]),
     "ppo_debug_pack_rows": (C.c_int, [C.c_int]),
+    "ppo_trainer_last_episodes": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "ppo_episode_tail": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int] + [C.c_void_p] * 4),
     "ppo_pack_rows": (C.c_int, [C.c_int64, C.c_int] + [C.c_void_p] * 8),
     "ppo_debug_rollout_timeline": (C.c_int, [C.c_void_p]),
     "ppo_device_count": (C.c_int, []),

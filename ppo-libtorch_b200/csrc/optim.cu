@@ -390,6 +390,76 @@ extern "C" int ppo_make_permutation(int64_t batch, uint64_t seed, uint64_t epoch
     return PPO_OK;
 }
 
+// The newest max_n finished episodes of an episode log (ppo_episode_tail): one CTA walks the [T,n] log backwards, 4096
+// rows per round (four independent loads per thread in flight; thread 0 / slot 0 = newest row), ranks the hits with ballot
+// prefixes and stops as soon as max_n are found - one round whenever episodes are shorter than ~40 steps on average.
+__global__ void __launch_bounds__(1024) episode_tail_kernel(const int32_t* __restrict__ fin_len,
+                                                            const float* __restrict__ fin_ret, int64_t rows, int max_n,
+                                                            int32_t* __restrict__ out_count, int32_t* __restrict__ out_len,
+                                                            float* __restrict__ out_ret) {
+    constexpr int U = 4;
+    __shared__ int32_t s_len[1024];
+    __shared__ float s_ret[1024];
+    __shared__ int s_warp[U * 32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int found = 0;   // CTA-uniform
+    for (int64_t hi = rows; hi > 0 && found < max_n; hi -= U * 1024) {
+        int32_t l[U];
+        float v[U];
+        bool any = false;
+#pragma unroll
+        for (int k = 0; k < U; k++) {
+            const int64_t r = hi - 1 - (k * 1024 + threadIdx.x);
+            l[k] = r >= 0 ? __ldg(fin_len + r) : 0;
+        }
+#pragma unroll
+        for (int k = 0; k < U; k++) {
+            const int64_t r = hi - 1 - (k * 1024 + threadIdx.x);
+            v[k] = l[k] ? __ldg(fin_ret + r) : 0.0f;
+            any |= l[k] != 0;
+        }
+        if (!__syncthreads_or(any)) continue;
+        unsigned b[U];
+#pragma unroll
+        for (int k = 0; k < U; k++) {
+            b[k] = __ballot_sync(0xffffffffu, l[k] != 0);
+            if (lane == 0) s_warp[k * 32 + w] = __popc(b[k]);
+        }
+        __syncthreads();
+        int base = found;   // rank of (slot k, warp w, lane 0); slots are ordered newest first
+#pragma unroll
+        for (int k = 0; k < U; k++) {
+            int off = 0, total = 0;
+            for (int i = 0; i < 32; i++) {
+                const int c = s_warp[k * 32 + i];
+                if (i < w) off += c;
+                total += c;
+            }
+            const int pos = base + off + __popc(b[k] & ((1u << lane) - 1u));
+            if (l[k] != 0 && pos < max_n) { s_len[pos] = l[k]; s_ret[pos] = v[k]; }
+            base += total;
+        }
+        found = base;
+        __syncthreads();
+    }
+    const int cnt = found < max_n ? found : max_n;
+    for (int i = threadIdx.x; i < cnt; i += 1024) {   // oldest first
+        out_len[i] = s_len[cnt - 1 - i];
+        out_ret[i] = s_ret[cnt - 1 - i];
+    }
+    if (threadIdx.x == 0) *out_count = cnt;
+}
+
+extern "C" int ppo_episode_tail(const int32_t* fin_len, const float* fin_ret, int64_t rows, int max_n, int32_t* out_count,
+                                int32_t* out_len, float* out_ret, ppo_stream_t stream) {
+    PPO_REQUIRE(rows >= 0 && max_n >= 1 && max_n <= 1024, "ppo_episode_tail: rows=%lld max_n=%d (1..1024)",
+                (long long)rows, max_n);
+    PPO_REQUIRE(out_count && out_len && out_ret && (rows == 0 || (fin_len && fin_ret)), "ppo_episode_tail: null buffer");
+    episode_tail_kernel<<<1, 1024, 0, as_stream(stream)>>>(fin_len, fin_ret, rows, max_n, out_count, out_len, out_ret);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
 // One 64-byte record per rollout row for the update kernel's gather (see ppo_pack_rows in the header)
 __global__ void pack_rows_kernel(int64_t batch, int O, const float* __restrict__ obs, const int32_t* __restrict__ actions,
                                  const float* __restrict__ logp, const float* __restrict__ adv,

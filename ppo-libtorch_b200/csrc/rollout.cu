@@ -86,8 +86,8 @@ __global__ void __launch_bounds__(MLP_THREADS) rollout_kernel(const RollArgs a) 
                     for (int j = 0; j < K; j++) a.mask_buf[row * K + j] = (uint8_t)((mbits >> j) & 1ull);
                 // stepEnvs (:413-483): step, truncate, auto-reset, episode statistics
                 float u[4] = {0.f, 0.f, 0.f, 0.f};
-                float reward, fr;
-                int32_t fl;
+                float reward, fr = 0.0f;
+                int32_t fl = 0;
                 StepOut so = Env::step(s, acts[0]);
                 len += 1;
                 ret = __fadd_rn(ret, so.reward);
@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(MLP_THREADS) rollout_kernel(const RollArgs a) 
                     len = 0; ret = 0.0f;
                 }
                 a.rewards_buf[row] = reward;
+                if (a.cfg.fin_len) { a.cfg.fin_len[row] = done ? fl : 0; a.cfg.fin_ret[row] = done ? fr : 0.0f; }
                 nd = done ? 1.0f : 0.0f;
             }
             // the next iteration's write to xs/ls/vs happens after the barriers inside net_forward
@@ -373,6 +374,8 @@ __global__ void __launch_bounds__(256, 2) rollout64_kernel(const RollArgs a) {
                 len += 1;
                 ret = __fadd_rn(ret, so.reward);
                 const bool done = so.terminated || (len == a.cfg.max_episode_steps);
+                const int32_t f_len = done ? len : 0;
+                const float f_ret = done ? ret : 0.0f;
                 if (done) {
                     fin_cnt += 1.0; fin_len += (double)len; fin_ret += (double)ret;
                     float u[4];
@@ -381,6 +384,7 @@ __global__ void __launch_bounds__(256, 2) rollout64_kernel(const RollArgs a) {
                     len = 0; ret = 0.0f;
                 }
                 a.rewards_buf[row] = so.reward;
+                if (a.cfg.fin_len) { a.cfg.fin_len[row] = f_len; a.cfg.fin_ret[row] = f_ret; }
                 nd = done ? 1.0f : 0.0f;
             }
             R64_TS(5);

@@ -342,6 +342,8 @@ __global__ void __launch_bounds__(RT_NWG * 128, 1) rollout_tc_kernel(const RollA
                 len += 1;
                 ret = __fadd_rn(ret, so.reward);
                 const bool fin = so.terminated || (len == a.cfg.max_episode_steps);
+                const int32_t f_len = fin ? len : 0;
+                const float f_ret = fin ? ret : 0.0f;
                 if (fin) {
                     fin_cnt += 1.0; fin_len += (double)len; fin_ret += (double)ret;
                     float u[4];
@@ -350,6 +352,7 @@ __global__ void __launch_bounds__(RT_NWG * 128, 1) rollout_tc_kernel(const RollA
                     len = 0; ret = 0.0f;
                 }
                 a.rewards_buf[row] = so.reward;
+                if (a.cfg.fin_len) { a.cfg.fin_len[row] = f_len; a.cfg.fin_ret[row] = f_ret; }
                 nd = fin ? 1.0f : 0.0f;
             }
         }

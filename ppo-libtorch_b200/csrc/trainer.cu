@@ -8,6 +8,7 @@
 //
 // With use_cuda_graph the whole iteration is captured once and replayed; the values that change
 // between iterations (learning rate, optimiser step, RNG counters) live in device scalars.
+#include <cstddef>
 #include <string.h>
 
 #include <map>
@@ -46,6 +47,9 @@ struct Readback {          // one D2H per iteration
     float ev, grad_norm;
     double ep_stats[3];
     unsigned peer_err, pad;
+    int32_t tail_count, pad2;            // newest finished episodes of the iteration, oldest first (ppo_episode_tail)
+    int32_t tail_len[PPO_EPISODE_TAIL];
+    float tail_ret[PPO_EPISODE_TAIL];
 };
 }  // namespace
 
@@ -68,6 +72,9 @@ struct ppo_trainer {
     float *adv_stats, *diag_hist, *ev_out, *norm_out;
     double *adv_partial, *ep_stats;
     void *upd_ws, *ev_ws, *adv_ws;
+    int32_t* fin_len = nullptr;   // episode log [T,N] + its tail {count, len[100], ret[100]}
+    float* fin_ret = nullptr;
+    int32_t* tail = nullptr;
     bool use_rec = false;
     float* rec = nullptr;   // packed rollout rows [B][16] (ppo_pack_rows) or nullptr when the shape has no packed form
     Scalars* d_scal;
@@ -196,6 +203,9 @@ extern "C" ppo_trainer* ppo_trainer_create(const ppo_trainer_cfg* c) {
         {"ev_ws", (void**)&t->ev_ws, (size_t)ppo_explained_variance_workspace_bytes()},
         {"adv_ws", (void**)&t->adv_ws,
          (size_t)ppo_adv_stats_workspace_bytes(t->n_mb * (c->update_epochs > 0 ? c->update_epochs : 1))},
+        {"fin_len", (void**)&t->fin_len, (size_t)T * N * 4},
+        {"fin_ret", (void**)&t->fin_ret, (size_t)T * N * 4},
+        {"tail", (void**)&t->tail, (size_t)(2 + 2 * PPO_EPISODE_TAIL) * 4},
         {"rec", (void**)&t->rec, (heads == 1 && !masked && O <= 4 && t->d.H == 64) ? (size_t)t->B * 64 : 0},
     };
     size_t total = 0;
@@ -354,6 +364,7 @@ static int phase_rollout(ppo_trainer* t, cudaStream_t st) {
     rc.use_gae = c.use_gae; rc.entropy_mode = c.hyper.entropy_mode; rc.masked = c.masked;
     rc.env_id_base = (uint32_t)c.rank * (uint32_t)c.num_envs; rc.seed = c.seed;
     rc.counter = 0; rc.d_counter = &t->d_scal->rollout_counter;
+    rc.fin_len = t->fin_len; rc.fin_ret = t->fin_ret;
     {
         PhaseTimer pt(t, PH_ROLLOUT, st);
         int r = ppo_rollout(t->params, &c.dims, &rc, t->state, t->ep_len, t->ep_ret, t->next_done, t->next_value,
@@ -395,9 +406,10 @@ static int phase_minibatch_grads(ppo_trainer* t, int mb, cudaStream_t st) {
     PPO_REQUIRE(cnt >= 1, "minibatch %d is empty", mb);
     const float inv_n = 1.0f / ((float)cnt * (float)c.world_size);
     PhaseTimer pt(t, PH_UPDATE, st);
-    return ppo_update_minibatch(t->params, &c.dims, t->obs, t->masks, t->actions, t->logprobs, t->adv, t->ret,
-                                t->values, t->perm, start, (int)cnt, inv_n, t->adv_stats + 2 * mb, &c.hyper, t->upd_ws,
-                                t->grads, t->grads + t->P, st);
+    return ppo::update_minibatch_fused(t->params, &c.dims, t->obs, t->masks, t->actions, t->logprobs, t->adv, t->ret,
+                                       t->values, t->perm, start, (int)cnt, inv_n, t->adv_stats + 2 * mb, &c.hyper,
+                                       t->upd_ws, t->grads, t->grads + t->P, nullptr, st, nullptr, nullptr,
+                                       t->use_rec ? t->rec : nullptr);
 }
 
 // single-GPU iterations: gradient + reduction + clip + AdamW back to back, the optimiser fused into the reduction launch
@@ -462,6 +474,14 @@ static int phase_tail(ppo_trainer* t, cudaStream_t st) {
     PPO_CUDA(cudaMemcpyAsync(&t->h_rb->ev, t->ev_out, 4, cudaMemcpyDeviceToHost, st));
     PPO_CUDA(cudaMemcpyAsync(&t->h_rb->grad_norm, t->norm_out, 4, cudaMemcpyDeviceToHost, st));
     PPO_CUDA(cudaMemcpyAsync(t->h_rb->ep_stats, t->ep_stats, 24, cudaMemcpyDeviceToHost, st));
+    // the episodes stepEnvs would have left in its CircularBuffer(100) (PPO/PPO_Discrete.cpp:474-480)
+    if ((rc = ppo_episode_tail(t->fin_len, t->fin_ret, t->B, PPO_EPISODE_TAIL, t->tail, t->tail + 2,
+                               reinterpret_cast<float*>(t->tail + 2 + PPO_EPISODE_TAIL), st)))
+        return rc;
+    static_assert(offsetof(Readback, tail_ret) - offsetof(Readback, tail_count) == (2 + PPO_EPISODE_TAIL) * 4,
+                  "Readback tail block mirrors the device tail buffer");
+    PPO_CUDA(cudaMemcpyAsync(&t->h_rb->tail_count, t->tail, (size_t)(2 + 2 * PPO_EPISODE_TAIL) * 4,
+                             cudaMemcpyDeviceToHost, st));
     if (t->peer_ready) PPO_CUDA(cudaMemcpyAsync(&t->h_rb->peer_err, t->peer.err, 4, cudaMemcpyDeviceToHost, st));
     return PPO_OK;
 }
@@ -485,6 +505,13 @@ static int enqueue_iteration(ppo_trainer* t, cudaStream_t st) {
             for (int mb = 0; mb < t->n_mb; mb++)
                 if ((rc = phase_minibatch_step(t, e, mb, st))) return rc;
         return phase_tail(t, st);
+    }
+    // split path inside iterate (NCCL data parallelism, profiling): same packed gather, rows indexed through `perm`
+    t->use_rec = t->rec && g_pack_rows && t->cfg.update_epochs > 0;
+    if (t->use_rec) {
+        PhaseTimer pt(t, PH_EPOCH, st);
+        if ((rc = ppo_pack_rows(t->B, t->d.O, t->obs, t->actions, t->logprobs, t->adv, t->ret, t->values, t->rec, st)))
+            return rc;
     }
     for (int e = 0; e < t->cfg.update_epochs; e++) {
         if ((rc = phase_begin_epoch(t, e, st))) return rc;
@@ -557,11 +584,21 @@ extern "C" int ppo_trainer_iterate(ppo_trainer* t, float h_lr, ppo_iter_result* 
 }
 
 // ---- split-phase API (host loops that interleave their own work between phases) ---------------------
+extern "C" int ppo_trainer_last_episodes(ppo_trainer* t, int max_n, int32_t* h_len, float* h_ret) {
+    if (!t || !h_len || !h_ret || max_n < 0) return 0;
+    int n = t->h_rb->tail_count;
+    if (n > PPO_EPISODE_TAIL) n = PPO_EPISODE_TAIL;
+    const int skip = n > max_n ? n - max_n : 0;   // keep the newest max_n
+    for (int i = skip; i < n; i++) { h_len[i - skip] = t->h_rb->tail_len[i]; h_ret[i - skip] = t->h_rb->tail_ret[i]; }
+    return n - skip;
+}
+
 extern "C" int ppo_trainer_rollout(ppo_trainer* t, float h_lr, ppo_stream_t stream) {
     PPO_REQUIRE(t, "null trainer");
     int rc = push_scalars(t, h_lr, as_stream(stream));
     if (rc) return rc;
     t->opt_in_iter = 0;
+    t->use_rec = false;   // the phase-by-phase API reads the row arrays (callers may edit them between phases)
     return phase_rollout(t, as_stream(stream));
 }
 extern "C" int ppo_trainer_begin_epoch(ppo_trainer* t, int epoch, ppo_stream_t stream) {

@@ -235,15 +235,14 @@ void PPOTrainerBase::train() {
         const ppo_iter_result r = iterate(lr);
         global_step += (uint64_t)m_batch_size;
         m_clipfracs.assign(1, r.clipfrac);              // already the mean over the update's minibatches (Utils.cpp:5-14)
-        // Episode statistics: the device returns {count, sum of lengths, sum of returns} of the episodes finished during
-        // this rollout, not each episode in env order (PPO_Discrete.cpp:474-480).  The last-100 ring is fed with
-        // min(count, 100) copies of the rollout's mean, which is what the ring's mean converges to whenever >= 100
-        // episodes finish per rollout; the per-episode order inside one rollout is not reproduced.
-        if (r.episodes > 0.0) {
-            const float mean_ret = (float)(r.ep_ret_sum / r.episodes);
-            const int64_t mean_len = (int64_t)(r.ep_len_sum / r.episodes + 0.5);
-            const int reps = r.episodes > 100.0 ? 100 : (int)r.episodes;
-            for (int i = 0; i < reps; i++) m_episode_stats->add(mean_ret, mean_len);
+        // Episode statistics (PPO_Discrete.cpp:474-480): the rollout kernel logs every finished episode at its (step, env)
+        // slot, ppo_episode_tail compacts the newest 100 on the device, and they are pushed oldest first - the ring ends
+        // up holding exactly what the reference's per-step pushes would have left in it.
+        {
+            int32_t lens[PPO_EPISODE_TAIL];
+            float rets[PPO_EPISODE_TAIL];
+            const int n = ppo_trainer_last_episodes(m_b200, PPO_EPISODE_TAIL, lens, rets);
+            for (int i = 0; i < n; i++) m_episode_stats->add(rets[i], (int64_t)lens[i]);
         }
         const auto now = std::chrono::steady_clock::now();
         const auto fps = std::chrono::duration_cast<std::chrono::milliseconds>(now - update_time);

@@ -143,9 +143,11 @@ def rollout(params, obs_dim, hidden, nvec, env_kind, state, ep_len, ep_ret, next
     out = dict(obs=f(T, n, obs_dim), actions=torch.empty((T, n, heads), dtype=torch.int32, device=dev),
                logprobs=f(T, n), rewards=f(T, n), dones=f(T, n), values=f(T, n), adv=f(T, n), ret=f(T, n),
                next_value=f(n), ep_stats=torch.zeros(3, dtype=torch.float64, device=dev),
-               masks=torch.empty((T, n, K), dtype=torch.uint8, device=dev) if masked else None)
+               masks=torch.empty((T, n, K), dtype=torch.uint8, device=dev) if masked else None,
+               fin_len=torch.empty((T, n), dtype=torch.int32, device=dev), fin_ret=f(T, n))
     cfg = RolloutCfg(env_kind, n, T, int(max_episode_steps), float(gamma), float(gae_lambda), int(use_gae),
-                     entropy_mode, int(masked), env_id_base, seed, counter, None)
+                     entropy_mode, int(masked), env_id_base, seed, counter, None, ptr(out["fin_len"]),
+                     ptr(out["fin_ret"]))
     check(load().ppo_rollout(ptr(params), C.byref(d), C.byref(cfg), ptr(state), ptr(ep_len), ptr(ep_ret),
                              ptr(next_done), ptr(out["next_value"]), ptr(out["obs"]), ptr(out["actions"]),
                              ptr(out["logprobs"]), ptr(out["rewards"]), ptr(out["dones"]), ptr(out["values"]),

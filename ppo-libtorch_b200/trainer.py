@@ -10,7 +10,8 @@ import torch
 from . import capi
 from .capi import Dims, Hyper, IterResult, TrainerCfg, check, load, stream_ptr
 
-_DT = {"actions": torch.int32, "perm": torch.int32, "ep_len": torch.int32, "masks": torch.uint8,
+_DT = {"actions": torch.int32, "perm": torch.int32, "ep_len": torch.int32, "masks": torch.uint8, "fin_len": torch.int32,
+       "tail": torch.int32,
        "ep_stats": torch.float64, "adv_partial": torch.float64}
 
 
@@ -96,6 +97,16 @@ class Trainer:
         out = np.empty(self.n_params, np.float32)
         check(load().ppo_trainer_get_params(self.h, out.ctypes.data_as(C.c_void_p)))
         return out
+
+    def last_episodes(self, max_n=100):
+        """(lengths int32[n], returns float32[n]) of the newest finished episodes of the last synchronised iteration,
+        oldest first, n <= min(max_n, 100): what the reference pushes into its CircularBuffer(100)
+        (PPO/PPO_Discrete.cpp:474-480)."""
+        lens = np.zeros(max(max_n, 1), np.int32)
+        rets = np.zeros(max(max_n, 1), np.float32)
+        n = load().ppo_trainer_last_episodes(self.h, int(max_n), lens.ctypes.data_as(C.c_void_p),
+                                             rets.ctypes.data_as(C.c_void_p))
+        return lens[:n].copy(), rets[:n].copy()
 
     def get_opt_state(self):
         m = np.empty(self.n_params, np.float32)

@@ -495,6 +495,9 @@ def test_fused_rollout_vs_oracle(P, orc, request, kind, O, nvec, masked, H, n, T
         st = obs_t.copy()
         oobs, orew, odone, ofl, ofr = orc.env_step(kind, st, o_len, o_ret, ga[:, 0].astype(np.int32), max_ep, ru)
         assert np.array_equal(o["rewards"][t], orew)
+        # episode log: length / return of the episode that finished at (t, env), zeros elsewhere
+        assert np.array_equal(o["fin_len"][t], np.asarray(ofl).astype(np.int32))
+        assert np.array_equal(o["fin_ret"][t], np.where(np.asarray(ofl) > 0, ofr, 0).astype(np.float32))
         nxt = o["obs"][t + 1] if t + 1 < T else state.cpu().numpy().T
         close(nxt, oobs, rtol=1e-6, atol=1e-7)
         prev_done = odone
@@ -663,3 +666,49 @@ def test_trainer_packed_rows_bit_identical(P, request):
     assert np.array_equal(out[0][0], out[1][0])
     assert np.array_equal(out[0][1][0], out[1][1][0]) and np.array_equal(out[0][1][1], out[1][1][1])
     assert out[0][2]["loss"] == out[1][2]["loss"]
+
+
+# ---------------------------------------------------------------------------------------------- episode tail (f2)
+@pytest.mark.parametrize("rows,density,max_n", [(0, 0.0, 100), (5, 1.0, 100), (5000, 0.001, 100), (5000, 0.0, 100),
+                                                (300000, 0.05, 100), (300000, 0.0005, 100), (70000, 0.3, 1024),
+                                                (4097, 0.5, 1)])
+def test_episode_tail_vs_numpy(P, rows, density, max_n):
+    """ppo_episode_tail = the newest max_n non-zero entries of the [T,n] episode log, oldest first: what
+    CircularBuffer(max_n) holds after the reference's per-step pushes (PPO/PPO_Discrete.cpp:474-480)."""
+    rng = np.random.default_rng(rows + max_n)
+    hit = rng.uniform(size=rows) < density
+    fl = np.where(hit, rng.integers(1, 500, size=rows), 0).astype(np.int32)
+    fr = np.where(hit, rng.standard_normal(rows) * 50, 0).astype(np.float32)
+    d_fl, d_fr = dev(fl) if rows else torch.zeros(1, dtype=torch.int32, device="cuda"), \
+        dev(fr) if rows else torch.zeros(1, device="cuda")
+    cnt = torch.full((1,), -1, dtype=torch.int32, device="cuda")
+    ol = torch.zeros(max_n, dtype=torch.int32, device="cuda")
+    orr = torch.zeros(max_n, device="cuda")
+    rc = P.capi.load().ppo_episode_tail(d_fl.data_ptr(), d_fr.data_ptr(), rows, max_n, cnt.data_ptr(), ol.data_ptr(),
+                                        orr.data_ptr(), None)
+    assert rc == 0, P.capi.last_error()
+    torch.cuda.synchronize()
+    idx = np.nonzero(fl)[0][-max_n:]
+    n = int(cnt.item())
+    assert n == len(idx)
+    assert np.array_equal(ol.cpu().numpy()[:n], fl[idx])
+    assert np.array_equal(orr.cpu().numpy()[:n], fr[idx])
+
+
+def test_trainer_last_episodes_feed_the_ring(P):
+    """Trainer.last_episodes() after iterate() = the tail of the trainer's own episode log; the per-iteration sums the
+    result struct reports are the sums over the whole log."""
+    tr = P.Trainer(num_envs=256, num_steps=64, num_minibatches=4, update_epochs=1, nvec=(2,), seed=3)
+    for _ in range(2):
+        res = tr.iterate(1e-3)
+        torch.cuda.synchronize()
+        fl = tr.buffer("fin_len").cpu().numpy().reshape(-1)
+        fr = tr.buffer("fin_ret").cpu().numpy().reshape(-1)
+        idx = np.nonzero(fl)[0]
+        assert len(idx) == int(res["episodes"]) and len(idx) > 100
+        assert int(fl.sum()) == int(res["ep_len_sum"])
+        lens, rets = tr.last_episodes()
+        assert np.array_equal(lens, fl[idx[-100:]]) and np.array_equal(rets, fr[idx[-100:]])
+        l5, r5 = tr.last_episodes(5)
+        assert np.array_equal(l5, fl[idx[-5:]]) and np.array_equal(r5, fr[idx[-5:]])
+    tr.close()
