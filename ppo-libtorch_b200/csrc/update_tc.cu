@@ -352,14 +352,14 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
             uint32_t pr[2] = {0u, 0u};
             const int nwg_total = gridDim.x * NWG;
             int tiles_done = 0;
-            if (blockIdx.x * NWG + g < ntiles) {
+            if (g * (int)gridDim.x + (int)blockIdx.x < ntiles) {
 #pragma unroll 1
                 for (int net = 0; net < 2; net++) {
                     mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
                     issue_stage<FMT, NWG, 4>(D, L, net, 0, wbars + net * 2, wbars + net * 2 + 1);
                 }
             }
-            for (int tile = blockIdx.x * NWG + g; tile < ntiles; tile += nwg_total) {
+            for (int tile = g * (int)gridDim.x + (int)blockIdx.x; tile < ntiles; tile += nwg_total) {
                 const bool has_next = tile + nwg_total < ntiles;
                 const int par = tiles_done & 1;
                 tiles_done++;
@@ -480,15 +480,15 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
             store8<FMT>(wg + L.xe[par_] + wt * 16, xe);
             store8<FMT>(wg + L.xe[par_] + TC_ROWS * 16 + wt * 16, lo);
         };
-        RowIn nxt = gather(blockIdx.x * NWG + g);
+        RowIn nxt = gather(g * (int)gridDim.x + (int)blockIdx.x);
         int tiles_done = 0;
-        if (blockIdx.x * NWG + g < ntiles) {   // G0 of the first tile
+        if (g * (int)gridDim.x + (int)blockIdx.x < ntiles) {   // G0 of the first tile
             stage_xe(nxt, 0);
             fence_async_smem();
             mbar_arrive(ready + 0);
             mbar_arrive(ready + 1);
         }
-        for (int tile = blockIdx.x * NWG + g; tile < ntiles; tile += nwg_total) {
+        for (int tile = g * (int)gridDim.x + (int)blockIdx.x; tile < ntiles; tile += nwg_total) {
             const RowIn cur = nxt;
             nxt = gather(tile + nwg_total);
             const bool has_next = tile + nwg_total < ntiles;
@@ -697,7 +697,7 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
         // warpgroups that owned no tile never wrote their accumulators: skip them
         int ng = 0;
         for (int g = 0; g < NWG; g++)
-            if (blockIdx.x * NWG + g < ntiles) ng = g + 1;
+            if (g * (int)gridDim.x + (int)blockIdx.x < ntiles) ng = g + 1;
         float v[64], w[64];
 #pragma unroll
         for (int g = 0; g < NWG; g++) {
@@ -818,7 +818,9 @@ static int launch_tc(const UpdArgs& a, int* grid_out, cudaStream_t st) {
     }
     const int ntiles = (a.mb_size + TC_ROWS - 1) / TC_ROWS;
     const int sms = sm_count() > 0 ? sm_count() : 148;
-    int grid = (ntiles + NWG - 1) / NWG;
+    // tiles are dealt CTA-first (warpgroup g of CTA b starts at tile g * grid + b): a partial last round leaves ONE
+    // busy warpgroup on many SMs instead of two on half as many
+    int grid = ntiles;
     if (grid > sms) grid = sms;
     if (grid > UPD_MAX_GRID) grid = UPD_MAX_GRID;
     update_tc_kernel<FMT, NWG, WIDE><<<grid, (NWG + 1) * 128, smem, st>>>(a);
