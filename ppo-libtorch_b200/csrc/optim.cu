@@ -269,7 +269,20 @@ __global__ void __launch_bounds__(ADV_THREADS) adv_moments_all_kernel(const floa
     const int64_t per = (cnt + ADV_SLICES - 1) / ADV_SLICES;
     const int64_t i0 = sl * per, i1 = i0 + per < cnt ? i0 + per : cnt;
     double s = 0.0, q = 0.0;
-    for (int64_t i = i0 + threadIdx.x; i < i1; i += ADV_THREADS) {
+    // four independent index evaluations + gathers in flight per thread; the sums are added in the same element order
+    // as the one-at-a-time loop (x0, x1, x2, x3 of a thread are consecutive terms of its chain)
+    int64_t i = i0 + threadIdx.x;
+    for (; i + 3 * ADV_THREADS < i1; i += 4 * ADV_THREADS) {
+        float x[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) x[u] = __ldg(adv + perm_index(start + i + u * ADV_THREADS, batch, half_bits, key));
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            s += (double)x[u];
+            q += (double)x[u] * (double)x[u];
+        }
+    }
+    for (; i < i1; i += ADV_THREADS) {
         const double x = (double)__ldg(adv + perm_index(start + i, batch, half_bits, key));
         s += x;
         q += x * x;
