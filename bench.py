@@ -391,7 +391,8 @@ def run_b200(args, wl_name):
     # {update, reduce, clip_adamw} (NCCL's own kernels are not counted: not ours).
     if world == 1 or not args.no_peer:
         packed = 1 if (wl["H"] == 64 and len(wl["nvec"]) == 1 and wl["O"] <= 4) else 0   # + ppo_pack_rows
-        launches = 4 + packed + wl["E"] * wl["MB"] * 2 + 1 + (1 if world > 1 else 0)
+        per_step = 2   # (1 with ppo_debug_fuse_tail(1) when min(tiles, 148) >= (n_par + 63) // 64: measured slower)
+        launches = 4 + packed + 1 + wl["E"] * wl["MB"] * per_step + 1 + (1 if world > 1 else 0)   # + episode tail
     else:
         launches = 3 + wl["E"] * (3 + wl["MB"] * 3) + 1
 

@@ -356,6 +356,10 @@ int ppo_debug_rollout_impl(int impl);
 /* 1 (default): trainers whose shape allows it (single head, unmasked, obs_dim <= 4) repack the rollout rows with
  * ppo_pack_rows once per iteration and the update kernel gathers records; 0: gather from the six row arrays. */
 int ppo_debug_pack_rows(int on);
+/* 1: on one GPU, when the update kernel's grid covers every 64-column block of the parameter vector, it runs the slab
+ * reduction + clip_grad_norm_ + AdamW itself behind a grid-wide barrier (one launch per optimiser step); 0 (default): the
+ * separate reduce_apply_kernel launch, which measured 1-2 % faster. */
+int ppo_debug_fuse_tail(int on);
 /* d_ts = device buffer of 8 int64 (NULL switches it off): CTA 0 / thread 0 of the hidden = 64 rollout kernel stamps the
  * SM clock at the six phase edges of rollout step 2 (tools/rollout_bench.py prints the deltas). */
 int ppo_debug_rollout_timeline(long long* d_ts);

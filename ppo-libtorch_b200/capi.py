@@ -79,6 +79,7 @@ _PROTOS = {
     "ppo_trainer_set_peers": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "ppo_debug_rollout_impl": (C.c_int, [C.c_int]),
     "ppo_debug_pack_rows": (C.c_int, [C.c_int]),
+    "ppo_debug_fuse_tail": (C.c_int, [C.c_int]),
     "ppo_trainer_last_episodes": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "ppo_episode_tail": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int] + [C.c_void_p] * 4),
     "ppo_pack_rows": (C.c_int, [C.c_int64, C.c_int] + [C.c_void_p] * 8),

@@ -560,9 +560,11 @@ int ppo::update_minibatch_fused(const float* params, const ppo_dims* dims, const
     const int mode = math_mode();
     if (mode != PPO_MATH_FP32) {  // tensor-core path when the shape fits its envelope, else the FMA kernels below
         int grid = 0;
-        const int rc = launch_update_tc(a, mode == PPO_MATH_BF16 ? 1 : 0, &grid, st);
+        bool tail_done = false;   // single GPU, enough CTAs: the update kernel reduces and steps by itself
+        const int rc = launch_update_tc(a, mode == PPO_MATH_BF16 ? 1 : 0, &grid, st, peer ? nullptr : fuse, grads_out,
+                                        diag_out, &tail_done);
         if (rc == PPO_OK) {
-            launch_reduce(a, grid, P, grads_out, diag_out, st, fuse, peer);
+            if (!tail_done) launch_reduce(a, grid, P, grads_out, diag_out, st, fuse, peer);
             PPO_LAUNCH_CHECK();
             return PPO_OK;
         }

@@ -10,6 +10,35 @@ constexpr int UPD_NDIAG = 8;       // pg, v, ent, kl, clip (+3 spare) partial su
 
 __host__ __device__ inline int64_t slab_stride(int P) { return ((int64_t)P + 31) & ~(int64_t)31; }
 
+// Optional tail of the slab reduction: clip_grad_norm_ + AdamW (PPO/PPO_Discrete.cpp:640-641) applied by the LAST reduce
+// CTA to finish (single-GPU path: no allreduce sits between the gradient and the optimiser, so reduce + norm + step are
+// one launch instead of two).  Workspace tail: ticket (zeroed once, left zeroed) + one double per reduce CTA.
+struct FuseAdam {
+    float* params;
+    float* exp_avg;
+    float* exp_avg_sq;
+    const float* d_lr;
+    float beta1, beta2, eps, weight_decay;
+    int64_t step_host;
+    const int64_t* d_step;
+    float max_grad_norm;
+    float* norm_out;
+    float* diag_hist;   // 8 floats of this optimiser step
+};
+// Slab reduction + clip + AdamW executed by the update kernel itself behind a grid-wide barrier (update_tc.cu:
+// fused_reduce_apply) instead of a second launch.  on != 0 only when every CTA of the launch is resident and there are at
+// least as many CTAs as 64-column blocks.  ticket: 16 uints (slots 2..4 used here), sq_part: one double per block.
+struct TailArgs {
+    int on, P;
+    int64_t stride;
+    float ent_coef, vf_coef;
+    float* grads_out;
+    float* diag_out;
+    FuseAdam f;
+    unsigned* ticket;
+    double* sq_part;
+};
+
 struct UpdArgs {
     const float* params;
     Dims d;
@@ -31,23 +60,9 @@ struct UpdArgs {
     ppo_hyper hp;
     float* slabs;    // [grid][slab_stride(P)]
     double* dpart;   // [grid][UPD_NDIAG]
+    TailArgs tail;
 };
 
-// Optional tail of the slab reduction: clip_grad_norm_ + AdamW (PPO/PPO_Discrete.cpp:640-641) applied by the LAST reduce
-// CTA to finish (single-GPU path: no allreduce sits between the gradient and the optimiser, so reduce + norm + step are
-// one launch instead of two).  Workspace tail: ticket (zeroed once, left zeroed) + one double per reduce CTA.
-struct FuseAdam {
-    float* params;
-    float* exp_avg;
-    float* exp_avg_sq;
-    const float* d_lr;
-    float beta1, beta2, eps, weight_decay;
-    int64_t step_host;
-    const int64_t* d_step;
-    float max_grad_norm;
-    float* norm_out;
-    float* diag_hist;   // 8 floats of this optimiser step
-};
 // Data-parallel variant of the fused tail: the allreduce happens INSIDE the reduction kernel over peer memory (NVLink
 // P2P loads of the other ranks' exchange buffers, mapped with CUDA IPC), so gradient exchange + clip + AdamW is one launch
 // per rank instead of reduce_kernel -> ncclAllReduce -> clip_adamw_kernel.  Exchange buffer of a rank (one cudaMalloc):
@@ -75,6 +90,8 @@ int update_minibatch_fused(const float* params, const ppo_dims* dims, const floa
 
 // update_tc.cu: returns PPO_ERR_UNSUPPORTED (without touching the error string) when the shape is outside the
 // tensor-core kernel's envelope (hidden != 64, obs_dim > 7, sumK > 32), PPO_OK after launching, else an error.
-int launch_update_tc(const UpdArgs& a, int fmt, int* grid_out, cudaStream_t st);
+// fuse != nullptr: the kernel may run the reduction + optimiser tail itself; *tail_done says whether it did
+int launch_update_tc(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st, const FuseAdam* fuse = nullptr,
+                     float* grads_out = nullptr, float* diag_out = nullptr, bool* tail_done = nullptr);
 
 }  // namespace ppo

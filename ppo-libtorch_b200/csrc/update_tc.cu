@@ -226,6 +226,136 @@ __device__ __forceinline__ void layer1_chunk(const float* P1, const float (&xe)[
     }
 }
 
+// ppo_debug_fuse_tail.  OFF by default: measured on B200 (config B, 148 CTAs) the in-kernel grid barriers cost as much as
+// the launch they save - 3.30-3.32 ms per iteration with the tail in the kernel against 3.26 ms with reduce_apply_kernel as
+// a second graph node - because the tail can only start after the slowest CTA either way.
+int g_fuse_tail = 0;
+
+// ---- fused tail: slab reduction + clip_grad_norm_ + AdamW behind a grid-wide barrier ------------------------------------
+// Every CTA of the launch is resident (grid <= SM count, one CTA per SM; the launcher checks), so the CTAs can wait for
+// each other on a global counter.  The spin is bounded: a CTA that never sees its peers falls through (wrong numbers, no
+// hang).  Same arithmetic and summation order as reduce_apply_kernel (update.cu), which stays the path for small grids.
+template <int NT>
+__device__ __forceinline__ void grid_arrive_wait(unsigned* ctr, int tid) {
+    __threadfence();   // this thread's global stores are visible device-wide before the CTA arrives
+    bar_sync(3, NT);
+    if (tid == 0) {
+        atomicAdd(ctr, 1u);
+        const long long t0 = clock64();
+        while (*reinterpret_cast<volatile unsigned*>(ctr) < gridDim.x) {
+            if (clock64() - t0 > 2000000000ll) break;
+        }
+        __threadfence();
+    }
+    bar_sync(3, NT);
+}
+
+template <int NT>
+__device__ void fused_reduce_apply(const UpdArgs& a, uint8_t* scratch, int tid) {
+    static_assert(NT == RED_COLS * RED_PARTS, "the tail is written for 256 threads");
+    const TailArgs& t = a.tail;
+    const FuseAdam& f = t.f;
+    double(*part)[RED_COLS] = reinterpret_cast<double(*)[RED_COLS]>(scratch);
+    double* shn = reinterpret_cast<double*>(scratch + RED_PARTS * RED_COLS * 8);
+    const int P = t.P, nslabs = (int)gridDim.x, nblocks = (P + RED_COLS - 1) / RED_COLS;
+    const int64_t stride = t.stride;
+    grid_arrive_wait<NT>(t.ticket + 2, tid);   // every slab and every dpart row of this launch is written
+    const int col = tid & (RED_COLS - 1), pt = tid / RED_COLS;
+    const int blk = (int)blockIdx.x;           // gridDim.x >= nblocks: at most one column block per CTA
+    const int i = blk * RED_COLS + col;
+    double acc = 0.0;
+    if (blk < nblocks && i < P) {
+        const int per = (nslabs + RED_PARTS - 1) / RED_PARTS;
+        const int s0 = pt * per, s1 = min(nslabs, s0 + per);
+        const float* p = a.slabs + (size_t)s0 * stride + i;
+        int sl = s0;
+        for (; sl + 4 <= s1; sl += 4, p += 4 * stride) {
+            const float a0 = __ldcg(p), a1 = __ldcg(p + stride), a2 = __ldcg(p + 2 * stride), a3 = __ldcg(p + 3 * stride);
+            acc += (double)a0; acc += (double)a1; acc += (double)a2; acc += (double)a3;
+        }
+        for (; sl < s1; sl++, p += stride) acc += (double)__ldcg(p);
+    }
+    part[pt][col] = acc;
+    bar_sync(3, NT);
+    double sq = 0.0;
+    if (pt == 0 && blk < nblocks && i < P) {
+        double tt = part[0][col];
+#pragma unroll
+        for (int q = 1; q < RED_PARTS; q++) tt += part[q][col];
+        const float g = (float)tt;
+        t.grads_out[i] = g;
+        sq = (double)g * (double)g;
+    }
+    if (tid < RED_COLS) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        if ((tid & 31) == 0) shn[tid >> 5] = sq;
+    }
+    if (blk == 0 && tid >= 64 && tid < 96) {   // diagnostics (warp 2 of block 0)
+        const int l = tid - 64;
+        double v = 0.0;
+        if (l < 5)
+            for (int sl = 0; sl < nslabs; sl++) v += __ldcg(a.dpart + (size_t)sl * UPD_NDIAG + l);
+        const double n_inv = (double)a.inv_n;
+        const float pg = (float)(__shfl_sync(0xffffffffu, v, 0) * n_inv);
+        const float vl = 0.5f * (float)(__shfl_sync(0xffffffffu, v, 1) * n_inv);
+        const float en = (float)(__shfl_sync(0xffffffffu, v, 2) * n_inv);
+        const float kl = (float)(__shfl_sync(0xffffffffu, v, 3) * n_inv);
+        const float cf = (float)(__shfl_sync(0xffffffffu, v, 4) * n_inv);
+        if (l < 8) {
+            const float d8[8] = {pg, vl, en, pg - t.ent_coef * en + vl * t.vf_coef, kl, cf, 0.0f, 0.0f};
+            float dv = 0.0f;
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+                if (q == l) dv = d8[q];
+            if (t.diag_out) t.diag_out[l] = dv;
+            if (f.diag_hist) f.diag_hist[l] = dv;
+        }
+    }
+    bar_sync(3, NT);
+    if (tid == 0 && blk < nblocks) t.sq_part[blk] = shn[0] + shn[1];
+    grid_arrive_wait<NT>(t.ticket + 3, tid);   // every block's squared-norm partial is published
+    double ss = 0.0;
+    for (int b = tid; b < nblocks; b += NT) ss += __ldcg(t.sq_part + b);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if ((tid & 31) == 0) shn[tid >> 5] = ss;
+    bar_sync(3, NT);
+    double tot = 0.0;
+#pragma unroll
+    for (int w = 0; w < NT / 32; w++) tot += shn[w];
+    const double norm = sqrt(tot);
+    if (tid == 0 && blk == 0 && f.norm_out) *f.norm_out = (float)norm;
+    const double coef = (double)f.max_grad_norm / (norm + 1e-6);
+    const float cf = (f.max_grad_norm > 0.0f && coef < 1.0) ? (float)coef : 1.0f;
+    const float lr = *f.d_lr;
+    const int64_t step = f.step_host + (f.d_step ? *f.d_step : 0);
+    const double b1 = (double)f.beta1, b2 = (double)f.beta2;
+    const double bc1 = 1.0 - pow(b1, (double)step);
+    const double bc2 = 1.0 - pow(b2, (double)step);
+    const float decay = (float)(1.0 - (double)lr * (double)f.weight_decay);
+    const float omb1 = (float)(1.0 - b1), omb2 = (float)(1.0 - b2);
+    const float sq_bc2 = (float)sqrt(bc2);
+    const float neg_step = (float)(-((double)lr / bc1));
+    if (blk < nblocks && tid < RED_COLS && i < P) {   // this CTA steps its own 64 columns
+        const int j = i;
+        float gg = __ldcg(t.grads_out + j);
+        if (cf != 1.0f) gg = __fmul_rn(gg, cf);
+        const float pv = __fmul_rn(f.params[j], decay);
+        const float mi = __fadd_rn(__fmul_rn(f.exp_avg[j], f.beta1), __fmul_rn(gg, omb1));
+        const float vi = __fadd_rn(__fmul_rn(f.exp_avg_sq[j], f.beta2), __fmul_rn(__fmul_rn(gg, gg), omb2));
+        f.exp_avg[j] = mi;
+        f.exp_avg_sq[j] = vi;
+        const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(vi), sq_bc2), f.eps);
+        f.params[j] = __fadd_rn(pv, __fmul_rn(neg_step, __fdiv_rn(mi, denom)));
+    }
+    // re-arm the counters for the next launch: the last CTA to leave has seen everybody pass both barriers
+    bar_sync(3, NT);
+    if (tid == 0 && atomicAdd(t.ticket + 4, 1u) == gridDim.x - 1) {
+        t.ticket[2] = 0u; t.ticket[3] = 0u; t.ticket[4] = 0u;
+    }
+}
+
 template <int FMT, int NWG, bool WIDE>
 __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const UpdArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -803,10 +933,14 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
     bar_sync(3, NWG * 128);
     TC_TS(4);
     if (warp == 0) tmem_dealloc(tmem, 512);
+    if constexpr (NWG * 128 == RED_COLS * RED_PARTS) {
+        if (a.tail.on) fused_reduce_apply<NWG * 128>(a, sm + L.wg0, tid);
+    }
 }
 
 template <int FMT, int NWG, bool WIDE>
-static int launch_tc(const UpdArgs& a, int* grid_out, cudaStream_t st) {
+static int launch_tc(UpdArgs& a, int* grid_out, cudaStream_t st, const FuseAdam* fuse, float* grads_out, float* diag_out,
+                     bool* tail_done) {
     const TcLayout L = tc_layout(a.d.K, NWG);
     const size_t smem = (size_t)L.end + 1024;
     PPO_REQUIRE(smem <= 227 * 1024, "update_tc: needs %zu B of shared memory", smem);
@@ -823,6 +957,17 @@ static int launch_tc(const UpdArgs& a, int* grid_out, cudaStream_t st) {
     int grid = ntiles;
     if (grid > sms) grid = sms;
     if (grid > UPD_MAX_GRID) grid = UPD_MAX_GRID;
+    a.tail.on = 0;
+    const int P = num_params(a.d.O, a.d.H, a.d.K);
+    if (fuse && g_fuse_tail && NWG * 128 == RED_COLS * RED_PARTS && grid <= sms && grid >= (P + RED_COLS - 1) / RED_COLS) {
+        char* tail = reinterpret_cast<char*>(a.dpart) + (size_t)UPD_MAX_GRID * UPD_NDIAG * sizeof(double);
+        a.tail.on = 1; a.tail.P = P; a.tail.stride = slab_stride(P);
+        a.tail.ent_coef = a.hp.ent_coef; a.tail.vf_coef = a.hp.vf_coef;
+        a.tail.grads_out = grads_out; a.tail.diag_out = diag_out; a.tail.f = *fuse;
+        a.tail.ticket = reinterpret_cast<unsigned*>(tail);
+        a.tail.sq_part = reinterpret_cast<double*>(tail + 64);
+    }
+    if (tail_done) *tail_done = a.tail.on != 0;
     update_tc_kernel<FMT, NWG, WIDE><<<grid, (NWG + 1) * 128, smem, st>>>(a);
     PPO_LAUNCH_CHECK();
     *grid_out = grid;
@@ -838,12 +983,24 @@ extern "C" int ppo_debug_tc_timeline(long long* d_ts, int who) {
     return PPO_OK;
 }
 namespace ppo {
-int launch_update_tc(const UpdArgs& a, int fmt, int* grid_out, cudaStream_t st) {
+int launch_update_tc(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st, const FuseAdam* fuse, float* grads_out,
+                     float* diag_out, bool* tail_done) {
+    if (tail_done) *tail_done = false;
     if (a.d.H != TC_H || a.d.O + 1 > 8 || a.d.K > TC_MAX_K) return PPO_ERR_UNSUPPORTED;
     if ((size_t)tc_layout(a.d.K, 2).end + 1024 > 227 * 1024) return PPO_ERR_UNSUPPORTED;
     const bool wide = a.d.O + 1 > 4;
-    if (fmt == FMT_BF16) return wide ? launch_tc<FMT_BF16, 2, true>(a, grid_out, st) : launch_tc<FMT_BF16, 2, false>(a, grid_out, st);
-    return wide ? launch_tc<FMT_F16, 2, true>(a, grid_out, st) : launch_tc<FMT_F16, 2, false>(a, grid_out, st);
+    if (fmt == FMT_BF16)
+        return wide ? launch_tc<FMT_BF16, 2, true>(a, grid_out, st, fuse, grads_out, diag_out, tail_done)
+                    : launch_tc<FMT_BF16, 2, false>(a, grid_out, st, fuse, grads_out, diag_out, tail_done);
+    return wide ? launch_tc<FMT_F16, 2, true>(a, grid_out, st, fuse, grads_out, diag_out, tail_done)
+                : launch_tc<FMT_F16, 2, false>(a, grid_out, st, fuse, grads_out, diag_out, tail_done);
 }
+}  // namespace ppo
+
+extern "C" int ppo_debug_fuse_tail(int on) {
+    ppo::g_fuse_tail = on;
+    return PPO_OK;
+}
+namespace ppo {
 
 }  // namespace ppo

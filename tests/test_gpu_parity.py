@@ -712,3 +712,23 @@ def test_trainer_last_episodes_feed_the_ring(P):
         l5, r5 = tr.last_episodes(5)
         assert np.array_equal(l5, fl[idx[-5:]]) and np.array_equal(r5, fr[idx[-5:]])
     tr.close()
+
+
+def test_trainer_in_kernel_tail_equals_reduce_apply_launch(P, request):
+    """ppo_debug_fuse_tail(1): the update kernel runs slab reduction + clip_grad_norm_ + AdamW itself behind a grid
+    barrier (needs >= 144 tiles per minibatch).  Same sums in the same order as reduce_apply_kernel: bit-identical."""
+    lib = P.capi.load()
+    request.addfinalizer(lambda: lib.ppo_debug_fuse_tail(0))
+    out = []
+    for on in (1, 0):
+        lib.ppo_debug_fuse_tail(on)
+        tr = P.Trainer(num_envs=2048, num_steps=64, num_minibatches=4, update_epochs=2, nvec=(2,), seed=5)
+        for _ in range(2):
+            res = tr.iterate(1e-3)
+        torch.cuda.synchronize()
+        out.append((tr.get_params().copy(), tr.get_opt_state(), res))
+        tr.close()
+    assert np.array_equal(out[0][0], out[1][0])
+    assert np.array_equal(out[0][1][0], out[1][1][0]) and np.array_equal(out[0][1][1], out[1][1][1])
+    for key in ("loss", "grad_norm", "approx_kl"):
+        assert out[0][2][key] == out[1][2][key], key
