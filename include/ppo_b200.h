@@ -360,6 +360,10 @@ int ppo_debug_pack_rows(int on);
  * reduction + clip_grad_norm_ + AdamW itself behind a grid-wide barrier (one launch per optimiser step); 0 (default): the
  * separate reduce_apply_kernel launch, which measured 1-2 % faster. */
 int ppo_debug_fuse_tail(int on);
+/* 1 (default): the update kernel and the reduction / optimiser kernel are launched with programmatic stream
+ * serialization (each calls griddepcontrol.wait before reading its predecessor's output), so a launch overlaps the tail
+ * of the kernel in front of it; 0: ordinary stream order. */
+int ppo_debug_pdl(int on);
 /* d_ts = device buffer of 8 int64 (NULL switches it off): CTA 0 / thread 0 of the hidden = 64 rollout kernel stamps the
  * SM clock at the six phase edges of rollout step 2 (tools/rollout_bench.py prints the deltas). */
 int ppo_debug_rollout_timeline(long long* d_ts);

@@ -67,6 +67,14 @@ using namespace ppo;
 
 extern "C" const char* ppo_last_error(void) { return g_err; }
 extern "C" int ppo_abi_version(void) { return PPO_B200_ABI_VERSION; }
+
+namespace ppo {
+int g_pdl = 1;
+}
+extern "C" int ppo_debug_pdl(int on) {
+    ppo::g_pdl = on;
+    return PPO_OK;
+}
 extern "C" int ppo_get_math_mode(void) { return g_math_mode; }
 extern "C" int ppo_set_math_mode(int mode) {
     PPO_REQUIRE(mode == PPO_MATH_FP32 || mode == PPO_MATH_BF16 || mode == PPO_MATH_FP16, "ppo_set_math_mode: mode=%d", mode);

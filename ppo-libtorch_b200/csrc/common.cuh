@@ -1,6 +1,7 @@
 // common.cuh — shared helpers for the sm_100a PPO kernels: error plumbing for the C ABI,
 // Philox4x32-10, the flat parameter-slab layout (reference order, PPO/Agent.cpp:41-66).
 #pragma once
+#include <utility>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -138,5 +139,25 @@ __device__ inline int64_t perm_index(int64_t i, int64_t batch, int half_bits, co
 }
 
 static inline cudaStream_t as_stream(ppo_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// ---- programmatic dependent launch (the per-minibatch kernel chain update -> reduce/AdamW -> update -> ...) --------------
+// A kernel launched with launch_pdl may be scheduled while its predecessor on the stream is still running; it must execute
+// pdl_wait() before touching anything the predecessor writes (the wait returns once the predecessor grid has completed
+// and its memory is visible).  pdl_trigger() in the predecessor lets the successor's launch proceed early.  Both are no-ops
+// for a kernel launched the ordinary way.  Captured into CUDA graphs as programmatic edges.
+extern int g_pdl;   // ppo_debug_pdl
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <class... KArgs, class... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = g_pdl ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
 
 }  // namespace ppo

@@ -177,6 +177,8 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_apply_kernel(
     __shared__ unsigned s_last;
     const int col = threadIdx.x & (RED_COLS - 1), pt = threadIdx.x / RED_COLS;
     const int i = blockIdx.x * RED_COLS + col;
+    pdl_trigger();   // the next update kernel may be scheduled behind this grid; it waits for our completion itself
+    pdl_wait();      // the update kernel's slabs are complete and visible
     double acc = 0.0;
     if (i < P) {
         const int per = (nslabs + RED_PARTS - 1) / RED_PARTS;
@@ -335,6 +337,8 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel
     const int64_t slot_off = (int64_t)(seq & 1u) * peer_slot_bytes(P);
     float* my_data = reinterpret_cast<float*>(pa.xchg[pa.rank] + slot_off);
     unsigned* my_flags = reinterpret_cast<unsigned*>(pa.xchg[pa.rank] + slot_off + px * 4);
+    pdl_trigger();
+    pdl_wait();
     double acc = 0.0;
     if (i < P) {
         const int per = (nslabs + RED_PARTS - 1) / RED_PARTS;
@@ -465,17 +469,17 @@ static inline void launch_reduce(const UpdArgs& a, int grid, int P, float* grads
     const int blocks = (P + RED_COLS - 1) / RED_COLS;
     if (fuse && peer) {
         char* tail = reinterpret_cast<char*>(a.dpart) + (size_t)UPD_MAX_GRID * UPD_NDIAG * sizeof(double);
-        reduce_peer_apply_kernel<<<blocks, RED_COLS * RED_PARTS, 0, st>>>(
-            a.slabs, a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out, *fuse,
-            *peer, reinterpret_cast<unsigned*>(tail), reinterpret_cast<double*>(tail + 64));
+        launch_pdl(reduce_peer_apply_kernel, dim3(blocks), dim3(RED_COLS * RED_PARTS), 0, st, (const float*)a.slabs,
+                   (const double*)a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out,
+                   *fuse, *peer, reinterpret_cast<unsigned*>(tail), reinterpret_cast<double*>(tail + 64));
         return;
     }
     if (fuse) {
         char* tail = reinterpret_cast<char*>(a.dpart) + (size_t)UPD_MAX_GRID * UPD_NDIAG * sizeof(double);
-        reduce_apply_kernel<<<blocks, RED_COLS * RED_PARTS, 0, st>>>(
-            a.slabs, a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out, *fuse,
-            reinterpret_cast<unsigned*>(tail), reinterpret_cast<double*>(tail + 64),
-            blocks <= (sm_count() > 0 ? sm_count() : 0));
+        launch_pdl(reduce_apply_kernel, dim3(blocks), dim3(RED_COLS * RED_PARTS), 0, st, (const float*)a.slabs,
+                   (const double*)a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out,
+                   *fuse, reinterpret_cast<unsigned*>(tail), reinterpret_cast<double*>(tail + 64),
+                   blocks <= (sm_count() > 0 ? sm_count() : 0));
         return;
     }
     reduce_kernel<<<blocks, RED_COLS * RED_PARTS, 0, st>>>(

@@ -368,16 +368,21 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + L.tmem_slot);
     const int ntiles = (a.mb_size + TC_ROWS - 1) / TC_ROWS;
     const int nthreads = (NWG + 1) * 128;   // NWG compute warpgroups + the MMA-issue warpgroup
-    long long* ts_buf = (blockIdx.x == 0 && tid == g_tc_ts_who) ? g_tc_ts : nullptr;
+    long long* ts_buf = (blockIdx.x == 0 && tid == (g_tc_ts_who & 0xFFFF)) ? g_tc_ts : nullptr;
+    // who | 0x40000000: thread 0 of EVERY CTA also stamps the global timer (ns) at entry / exit into slots 256 + 2 b + {0, 1}
+    long long* cta_ts = (g_tc_ts && (g_tc_ts_who & 0x40000000) && tid == 0) ? g_tc_ts + 256 + 2 * blockIdx.x : nullptr;
+    if (cta_ts) { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); cta_ts[0] = t; }
     TC_TS(0);
 
     // ---------------- prologue: tensor memory, barriers, parameters -> shared memory -------------------------
+    pdl_trigger();   // the reduction / optimiser kernel behind this one may be scheduled; it waits for our completion
     if (warp == 0) tmem_alloc(tmem_slot, 512);
     if (tid == 0) {
         for (int i = 0; i < NWG * 4; i++) mbar_init(bars + i, 1);   // [(g * 2 + net) * 2 + {doneZ, doneW}]
         for (int i = 0; i < NWG * 2; i++) mbar_init(bars + NWG * 4 + i, 128);   // ready[g * 2 + net]: operands staged
         mbar_init_fence();
     }
+    pdl_wait();      // the previous optimiser step's parameters (and everything older) are visible from here on
     {   // W2 of both nets as 16-bit activation-layout tiles: 1024 chunk tasks, all loads of a thread in flight together
         constexpr int W2_IT = (2 * 64 * 8 + (NWG + 1) * 128 - 1) / ((NWG + 1) * 128);
         float v[W2_IT][8];
@@ -932,6 +937,7 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
     tc_fence_before();
     bar_sync(3, NWG * 128);
     TC_TS(4);
+    if (cta_ts) { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); cta_ts[1] = t; }
     if (warp == 0) tmem_dealloc(tmem, 512);
     if constexpr (NWG * 128 == RED_COLS * RED_PARTS) {
         if (a.tail.on) fused_reduce_apply<NWG * 128>(a, sm + L.wg0, tid);
@@ -968,7 +974,7 @@ static int launch_tc(UpdArgs& a, int* grid_out, cudaStream_t st, const FuseAdam*
         a.tail.sq_part = reinterpret_cast<double*>(tail + 64);
     }
     if (tail_done) *tail_done = a.tail.on != 0;
-    update_tc_kernel<FMT, NWG, WIDE><<<grid, (NWG + 1) * 128, smem, st>>>(a);
+    launch_pdl(update_tc_kernel<FMT, NWG, WIDE>, dim3(grid), dim3((NWG + 1) * 128), smem, st, a);
     PPO_LAUNCH_CHECK();
     *grid_out = grid;
     return PPO_OK;

@@ -50,3 +50,23 @@ for who in (0, 32, 128):
             row.append(f"{names[k]}={t[b + k] - prev}")
             prev = t[b + k]
         print(f" tile {tile} (start +{t[b] - t[1]}): " + "  ".join(row))
+
+# per-CTA entry / exit on the global timer (ns) against the launch's CUDA-event duration
+ts = torch.zeros(1024, dtype=torch.int64, device="cuda")
+P.capi.check(lib.ppo_debug_tc_timeline(P.capi.ptr(ts), 0x40000000))
+for _ in range(3):
+    P.ops.update_minibatch(*args, **kw)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+ts.zero_()
+e0.record()
+P.ops.update_minibatch(*args, **kw)
+e1.record()
+torch.cuda.synchronize()
+P.capi.check(lib.ppo_debug_tc_timeline(None, 0))
+t = ts.cpu().numpy()[256:256 + 2 * 148].reshape(148, 2)
+t = t[t[:, 0] > 0]
+s0, s1 = t[:, 0] - t[:, 0].min(), t[:, 1] - t[:, 0].min()
+print(f"--- {len(t)} CTAs: entry spread {s0.max() / 1e3:.1f} us; exit min/median/max {s1.min() / 1e3:.1f} / "
+      f"{np.median(s1) / 1e3:.1f} / {s1.max() / 1e3:.1f} us after the first entry; "
+      f"update + reduce launches by events {e0.elapsed_time(e1) * 1e3:.1f} us")
