@@ -469,14 +469,14 @@ static inline void launch_reduce(const UpdArgs& a, int grid, int P, float* grads
     const int blocks = (P + RED_COLS - 1) / RED_COLS;
     if (fuse && peer) {
         char* tail = reinterpret_cast<char*>(a.dpart) + (size_t)UPD_MAX_GRID * UPD_NDIAG * sizeof(double);
-        launch_pdl(reduce_peer_apply_kernel, dim3(blocks), dim3(RED_COLS * RED_PARTS), 0, st, (const float*)a.slabs,
+        launch_pdl(false, reduce_peer_apply_kernel, dim3(blocks), dim3(RED_COLS * RED_PARTS), 0, st, (const float*)a.slabs,
                    (const double*)a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out,
                    *fuse, *peer, reinterpret_cast<unsigned*>(tail), reinterpret_cast<double*>(tail + 64));
         return;
     }
     if (fuse) {
         char* tail = reinterpret_cast<char*>(a.dpart) + (size_t)UPD_MAX_GRID * UPD_NDIAG * sizeof(double);
-        launch_pdl(reduce_apply_kernel, dim3(blocks), dim3(RED_COLS * RED_PARTS), 0, st, (const float*)a.slabs,
+        launch_pdl(true, reduce_apply_kernel, dim3(blocks), dim3(RED_COLS * RED_PARTS), 0, st, (const float*)a.slabs,
                    (const double*)a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out,
                    *fuse, reinterpret_cast<unsigned*>(tail), reinterpret_cast<double*>(tail + 64),
                    blocks <= (sm_count() > 0 ? sm_count() : 0));
@@ -540,6 +540,7 @@ int ppo::update_minibatch_fused(const float* params, const ppo_dims* dims, const
     UpdArgs a{};
     if (pf) a.pf = *pf;
     a.rec = reinterpret_cast<const float4*>(rec);
+    a.pdl = peer ? 0 : 1;   // measured on 2 GPUs: early launches next to the peer-polling kernel cost 7 % (4.03 vs 3.77 ms)
     if (peer) {
         Dims dd;
         if (int rc = make_dims(dims, &dd)) return rc;

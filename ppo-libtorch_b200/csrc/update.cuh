@@ -61,6 +61,7 @@ struct UpdArgs {
     float* slabs;    // [grid][slab_stride(P)]
     double* dpart;   // [grid][UPD_NDIAG]
     TailArgs tail;
+    int pdl;         // launch the tensor-core kernel with programmatic stream serialization (common.cuh: launch_pdl)
 };
 
 // Data-parallel variant of the fused tail: the allreduce happens INSIDE the reduction kernel over peer memory (NVLink

@@ -974,7 +974,7 @@ static int launch_tc(UpdArgs& a, int* grid_out, cudaStream_t st, const FuseAdam*
         a.tail.sq_part = reinterpret_cast<double*>(tail + 64);
     }
     if (tail_done) *tail_done = a.tail.on != 0;
-    launch_pdl(update_tc_kernel<FMT, NWG, WIDE>, dim3(grid), dim3((NWG + 1) * 128), smem, st, a);
+    launch_pdl(a.pdl != 0, update_tc_kernel<FMT, NWG, WIDE>, dim3(grid), dim3((NWG + 1) * 128), smem, st, a);
     PPO_LAUNCH_CHECK();
     *grid_out = grid;
     return PPO_OK;
