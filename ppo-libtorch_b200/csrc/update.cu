@@ -237,7 +237,11 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_apply_kernel(
             sq_part[blockIdx.x] = shn[0] + shn[1];
             __threadfence();
             atomicAdd(ticket, 1u);
-            while (*reinterpret_cast<volatile unsigned*>(ticket) < gridDim.x) __nanosleep(32);
+            const long long t0 = clock64();   // bounded: a CTA that never sees the others falls through (no GPU hang)
+            while (*reinterpret_cast<volatile unsigned*>(ticket) < gridDim.x) {
+                if (clock64() - t0 > 4000000000ll) break;
+                __nanosleep(32);
+            }
             __threadfence();
         }
         __syncthreads();
@@ -425,7 +429,11 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel
         sq_part[blockIdx.x] = shn[0] + shn[1];
         __threadfence();
         atomicAdd(ticket, 1u);
-        while (*reinterpret_cast<volatile unsigned*>(ticket) < gridDim.x) __nanosleep(32);
+        const long long t1 = clock64();
+        while (*reinterpret_cast<volatile unsigned*>(ticket) < gridDim.x) {
+            if (clock64() - t1 > 4000000000ll) { atomicExch(pa.err, 1u); break; }
+            __nanosleep(32);
+        }
         __threadfence();
     }
     __syncthreads();
