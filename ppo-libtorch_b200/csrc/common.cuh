@@ -112,25 +112,31 @@ struct PermFn {
     uint64_t seed, epoch;
     const uint64_t* d_epoch;   // optional device scalar added to `epoch` (CUDA-graph replay)
 };
+// Domain of the bijection = 2^bits with bits = ceil(log2(batch)) (>= 2): an UNBALANCED Feistel network (left half
+// bits / 2, right half the rest; the halves swap size every round and are back after four), so a power-of-two batch is
+// permuted without any cycle walking and any other batch rejects < 50 % of the draws.  (A balanced network needs an even
+// bit count: batch = 2^19 then walked a 2^20 domain, and a warp iterates until its slowest lane is inside - ~6 network
+// evaluations per index instead of 1.)  The field keeps its old name.
 __host__ inline int perm_half_bits(int64_t batch) {
     int bits = 2;
-    while (bits < 32 && (1ll << bits) < batch) bits += 2;
-    return bits / 2;
+    while (bits < 32 && (1ll << bits) < batch) bits++;
+    return bits;
 }
 __device__ inline void perm_keys(uint64_t seed, uint64_t epoch, uint32_t (&k)[4]) {
     Philox::gen(seed, 0x7065726Du /* 'perm' */, 3u, (uint32_t)epoch, (uint32_t)(epoch >> 32), k);
 }
-__device__ inline uint32_t feistel(uint32_t x, int half_bits, const uint32_t (&k)[4]) {
-    const uint32_t hm = (1u << half_bits) - 1u;
-    uint32_t l = x >> half_bits, r = x & hm;
+__device__ inline uint32_t feistel(uint32_t x, int bits, const uint32_t (&k)[4]) {
+    int lb = bits >> 1, rb = bits - lb;   // l: the high lb bits, r: the low rb bits
+    uint32_t l = x >> rb, r = x & ((1u << rb) - 1u);
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         uint32_t f = (r ^ k[i]) * 0x9E3779B1u;
         f ^= f >> 15; f *= 0x85EBCA77u; f ^= f >> 13;
-        const uint32_t nl = r, nr = l ^ (f & hm);
+        const uint32_t nl = r, nr = l ^ (f & ((1u << lb) - 1u));
         l = nl; r = nr;
+        const int t = lb; lb = rb; rb = t;
     }
-    return (l << half_bits) | r;
+    return (l << rb) | r;
 }
 __device__ inline int64_t perm_index(int64_t i, int64_t batch, int half_bits, const uint32_t (&k)[4]) {
     uint32_t x = (uint32_t)i;
