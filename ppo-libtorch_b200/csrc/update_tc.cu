@@ -35,39 +35,48 @@ constexpr int TC_ROWS = 128;        // rows per warpgroup tile
 constexpr int TC_MAX_K = 21;        // sum of logits (shared-memory budget of the per-row logit / db3 scratch)
 constexpr int ACT_BYTES = TC_ROWS * 128;  // one activation tile
 
+// Two-element members are stored as scalar pairs and read through selects: indexing a member ARRAY with a runtime `net`
+// put the whole struct in local memory (194 LDL/STL in the kernel, a dependent ~30-cycle load in front of every phase).
+#define TC_PAIR(name)                                                                     \
+    int name##_0, name##_1;                                                               \
+    __host__ __device__ __forceinline__ int name(int i) const { return i ? name##_1 : name##_0; }
 struct TcLayout {   // byte offsets into the 1024-aligned dynamic shared memory
-    int w2[2];      // 16-bit W2 of actor (0) and critic (1), 64 rows x 128 B each
+    TC_PAIR(w2)      // 16-bit W2 of actor (0) and critic (1), 64 rows x 128 B each
     int wg0, wg_stride;                  // per-warpgroup block
-    int a1[2], a2[2], xe[2], dout[2], lg, b3;   // offsets inside a warpgroup block ([net], XE: [tile parity])
-    int p1h[2];                          // 16-bit P1 = {W1|b1|0} as K chunks {hi, hi, lo, 0} [4][64 units][8]: B of the layer-1 MMAs
-    int p1[2], b2[2], w3[2], b3p[2];     // fp32 small parameters per net
+    TC_PAIR(a1) TC_PAIR(a2) TC_PAIR(xe) TC_PAIR(dout)   // offsets inside a warpgroup block ((net), XE: (tile parity))
+    int lg, b3;
+    TC_PAIR(p1h)     // 16-bit P1 = {W1|b1|0} as K chunks {hi, hi, lo, 0} [4][64 units][8]: B of the layer-1 MMAs
+    TC_PAIR(p1) TC_PAIR(b2) TC_PAIR(w3) TC_PAIR(b3p)    // fp32 small parameters per net
     int bars, tmem_slot, end;
     int ldo, n3a;                        // logits row stride (floats), padded actor logit count
 };
+#undef TC_PAIR
 __host__ __device__ inline TcLayout tc_layout(int K, int nwg) {
     TcLayout L;
     L.ldo = K | 1;
     L.n3a = (K + 7) & ~7;
-    L.w2[0] = 0;
-    L.w2[1] = 8192;
-    L.a1[0] = 0; L.a1[1] = ACT_BYTES; L.a2[0] = 2 * ACT_BYTES; L.a2[1] = 3 * ACT_BYTES;
-    L.xe[0] = 4 * ACT_BYTES; L.xe[1] = L.xe[0] + 2 * TC_ROWS * 16;   // per parity: 16-bit x (hi), then its residual (lo)
-    L.dout[0] = L.xe[1] + 2 * TC_ROWS * 16;
-    L.dout[1] = L.dout[0] + (L.n3a / 8) * TC_ROWS * 16;
-    L.lg = L.dout[1] + TC_ROWS * 16;
+    L.w2_0 = 0;
+    L.w2_1 = 8192;
+    L.a1_0 = 0; L.a1_1 = ACT_BYTES; L.a2_0 = 2 * ACT_BYTES; L.a2_1 = 3 * ACT_BYTES;
+    L.xe_0 = 4 * ACT_BYTES; L.xe_1 = L.xe_0 + 2 * TC_ROWS * 16;   // per parity: 16-bit x (hi), then its residual (lo)
+    L.dout_0 = L.xe_1 + 2 * TC_ROWS * 16;
+    L.dout_1 = L.dout_0 + (L.n3a / 8) * TC_ROWS * 16;
+    L.lg = L.dout_1 + TC_ROWS * 16;
     L.b3 = L.lg + ((TC_ROWS * L.ldo * 4 + 15) & ~15);
     L.wg_stride = (L.b3 + ((TC_ROWS * L.ldo * 4 + 15) & ~15) + 1023) & ~1023;
     L.wg0 = 16384;
     int o = L.wg0 + nwg * L.wg_stride;
-    for (int n = 0; n < 2; n++) {
-        const int k3 = n == 0 ? K : 1;
-        L.p1[n] = o; o += TC_H * 8 * 4;
-        L.b2[n] = o; o += TC_H * 4;
-        L.w3[n] = o; o += k3 * TC_H * 4;
-        L.b3p[n] = o; o += ((k3 + 3) & ~3) * 4;
-    }
+    L.p1_0 = o; o += TC_H * 8 * 4;
+    L.b2_0 = o; o += TC_H * 4;
+    L.w3_0 = o; o += K * TC_H * 4;
+    L.b3p_0 = o; o += ((K + 3) & ~3) * 4;
+    L.p1_1 = o; o += TC_H * 8 * 4;
+    L.b2_1 = o; o += TC_H * 4;
+    L.w3_1 = o; o += TC_H * 4;
+    L.b3p_1 = o; o += 4 * 4;
     o = (o + 127) & ~127;
-    for (int n = 0; n < 2; n++) { L.p1h[n] = o; o += 4 * TC_H * 16; }
+    L.p1h_0 = o; o += 4 * TC_H * 16;
+    L.p1h_1 = o; o += 4 * TC_H * 16;
     L.bars = o; o += 4 * 4 * 8;
     L.tmem_slot = o; o += 16;
     L.end = o;
@@ -140,7 +149,7 @@ __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int n
     const uint32_t fb = (uint32_t)net * 4u;
     const TcCols c = tc_cols(NWG, g, net, L.n3a);
     const uint32_t Z = tmem + (uint32_t)(g * 2 + net) * 64u;
-    const uint32_t A1 = wb + L.a1[net], A2 = wb + L.a2[net], W2 = sb + L.w2[net];
+    const uint32_t A1 = wb + L.a1(net), A2 = wb + L.a2(net), W2 = sb + L.w2(net);
     tc_fence_after();
     const bool lead = elect_one();
     if (ST == 0) {
@@ -152,7 +161,7 @@ __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int n
         }
     } else if (ST == 1) {
         const uint32_t acc0 = (fresh >> (fb + 3)) & 1u ? 0u : 1u;
-        const uint64_t da = act_desc_mnmajor(A2, 0), db = narrow_desc_mnmajor(wb + L.dout[net], TC_ROWS, 0);
+        const uint64_t da = act_desc_mnmajor(A2, 0), db = narrow_desc_mnmajor(wb + L.dout(net), TC_ROWS, 0);
         const uint32_t id = net == 0 ? idesc_f16(FMT, 64, L.n3a, 1, 1) : id_n8;
         if (lead) {
 #pragma unroll
@@ -163,7 +172,7 @@ __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int n
     } else if (ST == 2) {
         const uint64_t dak = act_desc_kmajor(A2, 0), dam = act_desc_mnmajor(A2, 0);
         const uint64_t dw = act_desc_mnmajor(W2, 0), dh = act_desc_mnmajor(A1, 0);
-        const uint64_t dx = narrow_desc_mnmajor(wb + L.xe[par], TC_ROWS, 0);
+        const uint64_t dx = narrow_desc_mnmajor(wb + L.xe(par), TC_ROWS, 0);
         const uint32_t acc0 = (fresh >> fb) & 1u ? 0u : 1u;
         if (lead) {
 #pragma unroll
@@ -178,20 +187,20 @@ __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int n
         }
         w.fresh &= ~(3u << fb);
     } else if (ST == 4) {
-        const uint64_t da = narrow_desc_kmajor(wb + L.xe[par], TC_ROWS * 16);          // {x.hi, x.lo}
-        const uint64_t db = narrow_desc_kmajor(sb + L.p1h[net], TC_H * 16);             // {P.hi, P.hi}
-        const uint64_t db2 = narrow_desc_kmajor(sb + L.p1h[net] + 2 * TC_H * 16, TC_H * 16);   // {P.lo, 0}
+        const uint64_t da = narrow_desc_kmajor(wb + L.xe(par), TC_ROWS * 16);          // {x.hi, x.lo}
+        const uint64_t db = narrow_desc_kmajor(sb + L.p1h(net), TC_H * 16);             // {P.hi, P.hi}
+        const uint64_t db2 = narrow_desc_kmajor(sb + L.p1h(net) + 2 * TC_H * 16, TC_H * 16);   // {P.lo, 0}
         if (lead) {
             mma_f16(Z, da, db, id_fwd, 0u);
             mma_f16(Z, da, db2, id_fwd, 1u);
             mma_commit(doneZ);
         }
     } else {
-        const uint64_t dam = act_desc_mnmajor(A2, 0), dx = narrow_desc_mnmajor(wb + L.xe[par], TC_ROWS, 0);
+        const uint64_t dam = act_desc_mnmajor(A2, 0), dx = narrow_desc_mnmajor(wb + L.xe(par), TC_ROWS, 0);
         const uint32_t acc0 = (fresh >> (fb + 2)) & 1u ? 0u : 1u;
-        const uint64_t da0 = narrow_desc_kmajor(wb + L.xe[par ^ 1], TC_ROWS * 16);
-        const uint64_t db0 = narrow_desc_kmajor(sb + L.p1h[net], TC_H * 16);
-        const uint64_t db1 = narrow_desc_kmajor(sb + L.p1h[net] + 2 * TC_H * 16, TC_H * 16);
+        const uint64_t da0 = narrow_desc_kmajor(wb + L.xe(par ^ 1), TC_ROWS * 16);
+        const uint64_t db0 = narrow_desc_kmajor(sb + L.p1h(net), TC_H * 16);
+        const uint64_t db1 = narrow_desc_kmajor(sb + L.p1h(net) + 2 * TC_H * 16, TC_H * 16);
         const bool g0 = __shfl_sync(0xffffffffu, (int)g0_next, 0) != 0;
         if (lead) {
             if (g0) {
@@ -398,7 +407,7 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
 #pragma unroll
         for (int it = 0; it < W2_IT; it++) {
             const int e = tid + it * nthreads;
-            if (e < 2 * 64 * 8) store8<FMT>(sm + L.w2[e >> 9] + act_chunk_off((e >> 3) & 63, e & 7), v[it]);
+            if (e < 2 * 64 * 8) store8<FMT>(sm + L.w2(e >> 9) + act_chunk_off((e >> 3) & 63, e & 7), v[it]);
         }
     }
     {   // fp32 small parameters: P1 = {W1 row, b1, 0..} [64][8], b2 [64], W3 [k3][64], b3 [k3] per net, one flat task list
@@ -415,20 +424,20 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
                 const float* src = nullptr;
                 if (e < S1) {
                     const int net = e >> 9, j = (e >> 3) & 63, i = e & 7;
-                    dst[u] = reinterpret_cast<float*>(sm + L.p1[net]) + (e & 511);
+                    dst[u] = reinterpret_cast<float*>(sm + L.p1(net)) + (e & 511);
                     if (i < O) src = a.params + offs[net].W1 + j * O + i;
                     else if (i == O) src = a.params + offs[net].b1 + j;
                 } else if (e < S2) {
                     const int t = e - S1, net = t >> 6;
-                    dst[u] = reinterpret_cast<float*>(sm + L.b2[net]) + (t & 63);
+                    dst[u] = reinterpret_cast<float*>(sm + L.b2(net)) + (t & 63);
                     src = a.params + offs[net].b2 + (t & 63);
                 } else if (e < S3) {
                     const int t = e - S2, net = t < 64 * K ? 0 : 1, idx = net ? t - 64 * K : t;
-                    dst[u] = reinterpret_cast<float*>(sm + L.w3[net]) + idx;
+                    dst[u] = reinterpret_cast<float*>(sm + L.w3(net)) + idx;
                     src = a.params + offs[net].W3 + idx;
                 } else {
                     const int t = e - S3, net = t < K ? 0 : 1, idx = net ? t - K : t;
-                    dst[u] = reinterpret_cast<float*>(sm + L.b3p[net]) + idx;
+                    dst[u] = reinterpret_cast<float*>(sm + L.b3p(net)) + idx;
                     src = a.params + offs[net].b3 + idx;
                 }
                 if (src) v[u] = __ldg(src);
@@ -457,7 +466,7 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
                 lo[i] = v[i] - unpack_lo<FMT>(ph);
                 lo[i + 1] = v[i + 1] - unpack_hi<FMT>(ph);
             }
-            uint8_t* dst = sm + L.p1h[net] + j * 16;
+            uint8_t* dst = sm + L.p1h(net) + j * 16;
             store8<FMT>(dst, v);
             store8<FMT>(dst + TC_H * 16, v);
             store8<FMT>(dst + 2 * TC_H * 16, lo);
@@ -484,13 +493,13 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
             D.wb = smem_u32(sm + L.wg0 + g * L.wg_stride); D.sb = smem_u32(sm); D.tmem = tmem; D.g = g; D.fresh = 0xFFu;
             uint64_t* wbars = bars + g * 4;
             uint64_t* ready = bars + NWG * 4 + g * 2;
-            uint32_t pr[2] = {0u, 0u};
+            uint32_t pr = 0u;   // bit net = phase parity of ready[net] (a bit mask, not an array: runtime-indexed arrays live in local memory)
             const int nwg_total = gridDim.x * NWG;
             int tiles_done = 0;
             if (g * (int)gridDim.x + (int)blockIdx.x < ntiles) {
 #pragma unroll 1
                 for (int net = 0; net < 2; net++) {
-                    mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
+                    mbar_wait(ready + net, (pr >> net) & 1u); pr ^= 1u << net;
                     issue_stage<FMT, NWG, 4>(D, L, net, 0, wbars + net * 2, wbars + net * 2 + 1);
                 }
             }
@@ -500,22 +509,22 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
                 tiles_done++;
 #pragma unroll 1
                 for (int net = 0; net < 2; net++) {
-                    mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
+                    mbar_wait(ready + net, (pr >> net) & 1u); pr ^= 1u << net;
                     issue_stage<FMT, NWG, 0>(D, L, net, par, wbars + net * 2, wbars + net * 2 + 1);
                 }
 #pragma unroll 1
                 for (int net = 0; net < 2; net++) {
-                    mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
+                    mbar_wait(ready + net, (pr >> net) & 1u); pr ^= 1u << net;
                     issue_stage<FMT, NWG, 1>(D, L, net, par, wbars + net * 2, wbars + net * 2 + 1);
                 }
 #pragma unroll 1
                 for (int net = 0; net < 2; net++) {
-                    mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
+                    mbar_wait(ready + net, (pr >> net) & 1u); pr ^= 1u << net;
                     issue_stage<FMT, NWG, 2>(D, L, net, par, wbars + net * 2, wbars + net * 2 + 1);
                 }
 #pragma unroll 1
                 for (int net = 0; net < 2; net++) {
-                    mbar_wait(ready + net, pr[net]); pr[net] ^= 1u;
+                    mbar_wait(ready + net, (pr >> net) & 1u); pr ^= 1u << net;
                     issue_stage<FMT, NWG, 3>(D, L, net, par, wbars + net * 2, wbars + net * 2 + 1, has_next);
                 }
             }
@@ -535,7 +544,7 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
         float* b3acc = reinterpret_cast<float*>(wg + L.b3) + wt * L.ldo; // this thread's actor db3 partials
         for (int q = 0; q < K; q++) b3acc[q] = 0.0f;
         uint64_t* wbars = bars + g * 4;          // [net * 2 + {doneZ, doneW}]
-        uint32_t pz[2] = {0u, 0u}, pw[2] = {0u, 0u};
+        uint32_t pz = 0u, pw = 0u;   // bit net = phase parity of doneZ / doneW of that net
         bool pendingW = false;                   // G4 of the previous tile not yet waited for (both nets)
         const bool masked = a.mask != nullptr;
         float meanf = 0.0f, stdf = 1.0f;
@@ -612,8 +621,8 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
                 lo[i] = xe[i] - unpack_lo<FMT>(ph);
                 lo[i + 1] = xe[i + 1] - unpack_hi<FMT>(ph);
             }
-            store8<FMT>(wg + L.xe[par_] + wt * 16, xe);
-            store8<FMT>(wg + L.xe[par_] + TC_ROWS * 16 + wt * 16, lo);
+            store8<FMT>(wg + L.xe(par_) + wt * 16, xe);
+            store8<FMT>(wg + L.xe(par_) + TC_ROWS * 16 + wt * 16, lo);
         };
         RowIn nxt = gather(g * (int)gridDim.x + (int)blockIdx.x);
         int tiles_done = 0;
@@ -638,9 +647,9 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
             // ---- P1: h1 = tanh(Z) (G0 = layer-1 pre-activations incl. bias, issued one tile ahead) -> A1[net]; G1
 #pragma unroll 1
             for (int net = 0; net < 2; net++) {
-                uint8_t* A1 = wg + L.a1[net];
+                uint8_t* A1 = wg + L.a1(net);
                 uint64_t* doneZ = wbars + net * 2;
-                mbar_wait(doneZ, pz[net]); pz[net] ^= 1u;
+                mbar_wait(doneZ, (pz >> net) & 1u); pz ^= 1u << net;
                 tc_fence_after();
                 const uint32_t zaddr = tmem_addr(tmem, (uint32_t)w4 * 32u, (uint32_t)(g * 2 + net) * 64u);
 #pragma unroll
@@ -665,15 +674,15 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
 #pragma unroll 1
             for (int net = 0; net < 2; net++) {
                 const int k3 = net == 0 ? K : 1;
-                const float* B2 = reinterpret_cast<const float*>(sm + L.b2[net]);
-                const float* W3 = reinterpret_cast<const float*>(sm + L.w3[net]);
-                const float* B3 = reinterpret_cast<const float*>(sm + L.b3p[net]);
-                uint8_t *A2 = wg + L.a2[net], *DO = wg + L.dout[net];
+                const float* B2 = reinterpret_cast<const float*>(sm + L.b2(net));
+                const float* W3 = reinterpret_cast<const float*>(sm + L.w3(net));
+                const float* B3 = reinterpret_cast<const float*>(sm + L.b3p(net));
+                uint8_t *A2 = wg + L.a2(net), *DO = wg + L.dout(net);
                 uint64_t *doneZ = wbars + net * 2, *doneW = doneZ + 1;
                 if (pendingW) {  // G4 of the previous tile has read A2[net]
-                    mbar_wait(doneW, pw[net]); pw[net] ^= 1u;
+                    mbar_wait(doneW, (pw >> net) & 1u); pw ^= 1u << net;
                 }
-                mbar_wait(doneZ, pz[net]); pz[net] ^= 1u;
+                mbar_wait(doneZ, (pz >> net) & 1u); pz ^= 1u << net;
                 tc_fence_after();
                 TC_TS(tsb + 7 + net * 4);
                 float h2[64];
@@ -738,8 +747,8 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
 #pragma unroll 1
             for (int net = 0; net < 2; net++) {
                 const int k3 = net == 0 ? K : 1;
-                const float* W3 = reinterpret_cast<const float*>(sm + L.w3[net]);
-                uint8_t* A2 = wg + L.a2[net];
+                const float* W3 = reinterpret_cast<const float*>(sm + L.w3(net));
+                uint8_t* A2 = wg + L.a2(net);
                 uint64_t *doneZ = wbars + net * 2, *doneW = doneZ + 1;
                 float d[64];
 #pragma unroll
@@ -761,7 +770,7 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
                     for (int i = 0; i < 8; i++) d[c * 8 + i] *= fmaf(-h2[i], h2[i], 1.0f);
                 }
                 TC_TS(tsb + 15 + net * 4);
-                mbar_wait(doneW, pw[net]); pw[net] ^= 1u;  // G5 has read A2 / DO
+                mbar_wait(doneW, (pw >> net) & 1u); pw ^= 1u << net;  // G5 has read A2 / DO
                 TC_TS(tsb + 16 + net * 4);
 #pragma unroll
                 for (int c = 0; c < 8; c++) store8<FMT>(A2 + act_chunk_off(wt, c), d + c * 8);
@@ -773,11 +782,11 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
             // ---- P4: dZ1 = Z * (1 - h1^2) -> A2[net] (once G2 / G3 have read dZ2); G4
 #pragma unroll 1
             for (int net = 0; net < 2; net++) {
-                uint8_t *A1 = wg + L.a1[net], *A2 = wg + L.a2[net];
+                uint8_t *A1 = wg + L.a1(net), *A2 = wg + L.a2(net);
                 uint64_t *doneZ = wbars + net * 2, *doneW = doneZ + 1;
                 if (net == 0 && has_next) stage_xe(nxt, par ^ 1);   // XE[par ^ 1]: last read by the previous tile's G4
                 TC_TS(tsb + 23 + net * 6);
-                mbar_wait(doneZ, pz[net]); pz[net] ^= 1u;
+                mbar_wait(doneZ, (pz >> net) & 1u); pz ^= 1u << net;
                 tc_fence_after();
                 TC_TS(tsb + 24 + net * 6);
                 float d[64];
@@ -793,7 +802,7 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
                     for (int i = 0; i < 8; i++) d[c * 8 + i] *= fmaf(-h1[i], h1[i], 1.0f);
                 }
                 TC_TS(tsb + 25 + net * 6);
-                mbar_wait(doneW, pw[net]); pw[net] ^= 1u;  // G3 has read A1 / A2
+                mbar_wait(doneW, (pw >> net) & 1u); pw ^= 1u << net;  // G3 has read A1 / A2
                 TC_TS(tsb + 26 + net * 6);
 #pragma unroll
                 for (int c = 0; c < 8; c++) store8<FMT>(A2 + act_chunk_off(wt, c), d + c * 8);
@@ -806,8 +815,8 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
             pendingW = true;
         }
         if (pendingW) {
-            mbar_wait(wbars + 1, pw[0]);
-            mbar_wait(wbars + 3, pw[1]);
+            mbar_wait(wbars + 1, pw & 1u);
+            mbar_wait(wbars + 3, (pw >> 1) & 1u);
         }
     }
 
