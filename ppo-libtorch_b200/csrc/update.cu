@@ -329,7 +329,8 @@ __device__ __forceinline__ void st_sys_u32(unsigned* p, unsigned v) {
 }
 __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel(
     const float* __restrict__ slabs, const double* __restrict__ dpart, int nslabs, int P, int64_t stride, float inv_n,
-    float ent_coef, float vf_coef, float* grads_out, float* __restrict__ diag_out, const FuseAdam f, const PeerArgs pa,
+    float ent_coef, float vf_coef, float* grads_out, float* __restrict__ diag_out, const FuseAdam f,
+    const __grid_constant__ PeerArgs pa,   // indexed with runtime ranks: read from the constant bank, not a local copy
     unsigned* ticket, double* sq_part) {
     __shared__ double part[RED_PARTS][RED_COLS];
     __shared__ double shn[RED_COLS * RED_PARTS / 32];
