@@ -33,9 +33,9 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "cartpole_4096x128_h64"
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE update-kernel launch from an `ncu --set full` capture of this
-# command (profiles/r01p_update_tc_ncu.txt, cold L2): 14.83 MB + 10 KB.  Algorithmic bytes per launch are 131072 rows x
+# command (profiles/r01r_update_tc_ncu.txt, cold L2): 14.82 MB.  Algorithmic bytes per launch are 131072 rows x
 # 36 B = 4.7 MB, fetched as 64-byte packed records = 8.4 MB (ppo_pack_rows), + 37 KB of parameters per CTA.
-NCU_TRAFFIC = {("cartpole_4096x128_h64", 2): 14.83e6 + 10.5e3}
+NCU_TRAFFIC = {("cartpole_4096x128_h64", 2): 14.82e6}
 HYPER = dict(gamma=0.98, gae_lambda=0.95, clip_coef=0.2, norm_adv=True, clip_vloss=True, ent_coef=0.0, vf_coef=0.5,
              max_grad_norm=0.5)
 LR0 = 1e-3
