@@ -38,6 +38,9 @@ class Hyper(C.Structure):
                 ("ent_coef", C.c_float), ("vf_coef", C.c_float), ("entropy_mode", C.c_int32)]
 
 
+ABI_VERSION = 3   # PPO_B200_ABI_VERSION in include/ppo_b200.h (3: episode log fields in ppo_rollout_cfg)
+
+
 class RolloutCfg(C.Structure):
     _fields_ = [("env_kind", C.c_int32), ("n_envs", C.c_int32), ("n_steps", C.c_int32),
                 ("max_episode_steps", C.c_int32), ("gamma", C.c_float), ("gae_lambda", C.c_float),

@@ -152,3 +152,14 @@ def test_driver_refuses_to_run_without_cuda(tmp_path):
         (tmp_path / "PPOConfig.toml").write_text(CARTPOLE_TOML.replace("use_cuda = false", "use_cuda = true"))
         p = subprocess.run([exe], cwd=tmp_path, capture_output=True, text=True, timeout=120)
         assert p.returncode == 1 and "no CUDA device" in p.stdout
+
+
+def test_abi_version_matches_header():
+    """capi.ABI_VERSION (what __graft_entry__.build() asserts) = PPO_B200_ABI_VERSION in the header = what the library
+    reports."""
+    import re
+    import ppo_libtorch_b200 as P
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "ppo_b200.h")).read()
+    v = int(re.search(r"#define\s+PPO_B200_ABI_VERSION\s+(\d+)", hdr).group(1))
+    assert v == P.capi.ABI_VERSION == P.capi.load().ppo_abi_version()
