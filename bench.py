@@ -4,10 +4,12 @@
     python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
     python bench.py --impl reference --steps K --warmup W    # the reference's own CPU path (oracle/_ref/ppo_ref)
 
-A "step" is one PPO iteration of BASELINE.json configs[1] per GPU: CartPole PPO_Discrete, 4096 envs x 128
-steps, 2x64 MLP, E=10 epochs x 4 minibatches (CartPoleRecommendedSettings.toml hyper-parameters, action_size=2).
-N>1 (torchrun, one rank per GPU): envs shard by rank (weak scaling, 4096 envs per GPU), gradients and advantage
-moments are allreduced over NCCL.  Rank 0 prints ONE JSON line.
+A "step" is one PPO iteration of BASELINE.json configs[4] (the north-star shape): CartPole PPO_Discrete,
+1 048 576 envs x 128 steps IN TOTAL, 2x64 MLP, E=10 epochs x 4 minibatches (CartPoleRecommendedSettings.toml
+hyper-parameters, action_size=2).  N>1 (torchrun, one rank per GPU): the envs shard by rank (STRONG scaling,
+1 048 576 / N envs per GPU); per optimiser step the gradient is exchanged over NVLink peer memory, the advantage
+moments go through one NCCL allreduce per iteration.  The latency-bound point, configs[1] (4096 envs x 128 steps per
+GPU, weak), is measured in the same run and reported under "config_b".  Rank 0 prints ONE JSON line.
 """
 import argparse
 import json
@@ -28,10 +30,14 @@ WORKLOADS = {
     # name: env, O, nvec, H, envs per GPU, steps, minibatches, epochs, max_episode_steps
     "cartpole_4096x128_h64": dict(env=0, O=4, nvec=(2,), H=64, N=4096, T=128, MB=4, E=10, max_ep=500),
     "cartpole_131072x128_h64": dict(env=0, O=4, nvec=(2,), H=64, N=131072, T=128, MB=4, E=10, max_ep=500),
+    # total=True: N is the WHOLE job's env count, sharded N / world per GPU (strong scaling)
+    "cartpole_1048576x128_h64": dict(env=0, O=4, nvec=(2,), H=64, N=1048576, T=128, MB=4, E=10, max_ep=500, total=True),
     "mountaincar_65536x256_h256": dict(env=1, O=2, nvec=(3,), H=256, N=65536, T=256, MB=4, E=10, max_ep=200),
     "cartpole_8x32_h64": dict(env=0, O=4, nvec=(2,), H=64, N=8, T=32, MB=4, E=10, max_ep=500),
 }
-DEFAULT_WORKLOAD = "cartpole_4096x128_h64"
+DEFAULT_WORKLOAD = "cartpole_1048576x128_h64"
+CONFIG_B = "cartpole_4096x128_h64"
+REF_SAMPLE_ENVS = 32768   # env count the CPU arm runs when the workload itself would take hours on host cores
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE update-kernel launch from an `ncu --set full` capture of this
 # command (profiles/r01r_update_tc_ncu.txt, cold L2): 14.82 MB.  Algorithmic bytes per launch are 131072 rows x
 # 36 B = 4.7 MB, fetched as 64-byte packed records = 8.4 MB (ppo_pack_rows), + 37 KB of parameters per CTA.
@@ -117,13 +123,24 @@ def run_reference(args, wl_name):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    wl = WORKLOADS[wl_name]
+    wl = dict(WORKLOADS[wl_name])
     binary = os.path.join(ROOT, "oracle", "_ref", "ppo_ref")
     cores = os.cpu_count() or 1
+    total = bool(wl.get("total"))
     base = {"impl": "reference", "metric": "env_steps_per_sec", "unit": "env-steps/s", "n_gpus": args.gpus,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "strong" if total else "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
             "config": {"workload": wl_name, "envs": wl["N"], "rollout_steps": wl["T"], "hidden": wl["H"],
                        "update_epochs": wl["E"], "minibatches": wl["MB"]}}
+    ref_envs = wl["N"]
+    if total and wl["N"] > REF_SAMPLE_ENVS:
+        # 1 048 576 envs x 128 steps = 134 M env-steps per update: ~15 min per update on host cores.  The CPU arm runs
+        # the same PPO update on a REF_SAMPLE_ENVS-env shard of it (its env-steps/s is flat in the env count from a few
+        # thousand envs up: per-env ThreadPool jobs and per-sample LibTorch work both scale linearly) and the rate is
+        # quoted for the workload as is.
+        ref_envs = REF_SAMPLE_ENVS
+        wl["N"] = ref_envs
+        base["config"]["reference_sample_envs"] = ref_envs
     if not os.path.exists(binary):
         print(json.dumps(dict(base, unavailable="oracle/_ref/ppo_ref not built (needs /root/reference at build time)")))
         return 0
@@ -165,8 +182,10 @@ max_grad_norm = {HYPER['max_grad_norm']}
     with open(os.path.join(tmp, "PPOConfig.toml"), "w") as f:
         f.write(toml)
     t0 = time.time()
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: the LibTorch CPU update must see every host core
+    env = {k: v for k, v in os.environ.items() if k not in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OMP_PROC_BIND")}
     try:
-        out = subprocess.run([binary], cwd=tmp, capture_output=True, text=True, timeout=1500).stdout
+        out = subprocess.run([binary], cwd=tmp, capture_output=True, text=True, timeout=1500, env=env).stdout
     except subprocess.TimeoutExpired as e:
         out = (e.stdout or b"").decode() if isinstance(e.stdout, bytes) else (e.stdout or "")
     wall = time.time() - t0
@@ -179,9 +198,10 @@ max_grad_norm = {HYPER['max_grad_norm']}
     ms = [batch / f * 1000.0 for f in timed]
     ms_per_step = sum(ms) / len(ms)
     value = batch / (ms_per_step / 1000.0)
-    sample = (f"{len(timed)} PPO update(s) of {batch} env-steps each after {warm} warm-up update(s) "
-              f"(requested {args.steps}+{args.warmup}, bounded to {updates}); self-reported per-update fps of "
-              f"the unmodified reference binary; wall {wall:.1f} s")
+    sample = (f"{len(timed)} PPO update(s) of {batch} env-steps each ({ref_envs} envs x {wl['T']} steps) after {warm} "
+              f"warm-up update(s) (requested {args.steps}+{args.warmup}, bounded to {updates}); self-reported "
+              f"per-update fps of the unmodified reference binary on {cores} host cores (OMP/MKL thread caps removed "
+              f"from its environment); wall {wall:.1f} s")
     line = dict(base, value=value, steps=len(timed), warmup=warm, ms_per_step=ms_per_step,
                 cpu_baseline={"value": value, "unit": "env-steps/s", "cores": cores, "kind": "reference",
                               "sample": sample},
@@ -254,9 +274,23 @@ def kernel_rooflines(P, torch, pk):
                                       P.capi.ptr(act), 500, None, 1, 7, P.capi.ptr(bufs[0]), P.capi.ptr(bufs[1]),
                                       P.capi.ptr(bufs[2]), None, None, P.capi.stream_ptr()))
     ms = timeit(step)
-    by = (60.0 - 8.0 + 16.0) * n      # no fin_len/fin_ret outputs here (-8), + obs row (+16)
+    by = (60.0 + 16.0) * n      # 60 B/env-step (state r+w 32, action 4, reward 4, done 4, ep_len + ep_ret r+w 16) + 16 B obs row
     out["env_step_cartpole"] = {"envs": n, "ms": ms, "bytes": by, "achieved": by / ms / 1e6, "peak": pk["hbm"],
                                 "unit": "GB/s", "frac": by / ms / 1e6 / pk["hbm"]}
+    del state, ep_len, ep_ret, obs, act, bufs
+    # env step, MountainCar, 16M envs (44 B/env-step: state r+w 16, action 4, reward 4, done 4, counters r+w 16; + 8 B obs row)
+    state, ep_len, ep_ret, obs = P.ops.env_reset(P.ENV_MOUNTAINCAR, n, seed=1)
+    act = torch.randint(0, 3, (n,), device=dev, dtype=torch.int32)
+    bufs = [torch.empty((n, 2), device=dev), torch.empty(n, device=dev), torch.empty(n, device=dev)]
+
+    def step_mc():
+        P.capi.check(lib.ppo_env_step(1, n, P.capi.ptr(state), P.capi.ptr(ep_len), P.capi.ptr(ep_ret),
+                                      P.capi.ptr(act), 200, None, 1, 7, P.capi.ptr(bufs[0]), P.capi.ptr(bufs[1]),
+                                      P.capi.ptr(bufs[2]), None, None, P.capi.stream_ptr()))
+    ms = timeit(step_mc)
+    by = (44.0 + 8.0) * n
+    out["env_step_mountaincar"] = {"envs": n, "ms": ms, "bytes": by, "achieved": by / ms / 1e6, "peak": pk["hbm"],
+                                   "unit": "GB/s", "frac": by / ms / 1e6 / pk["hbm"]}
     del state, ep_len, ep_ret, obs, act, bufs
     # categorical, masked, nvec {3,3,3,3,3,2,2,2}, 4M rows (145 B/row, Philox uniforms)
     n, nvec = 1 << 22, [3, 3, 3, 3, 3, 2, 2, 2]
@@ -274,11 +308,88 @@ def kernel_rooflines(P, torch, pk):
     by = 145.0 * n
     out["categorical_masked_k21"] = {"rows": n, "ms": ms, "bytes": by, "achieved": by / ms / 1e6, "peak": pk["hbm"],
                                      "unit": "GB/s", "frac": by / ms / 1e6 / pk["hbm"]}
+    # the same at BASELINE configs[3]'s own size (262 144 rows, 38 MB: L2-resident and launch-latency sized)
+    full = n
+    n = 262144
+    ms = timeit(cat, iters=50)
+    by = 145.0 * n
+    out["categorical_masked_k21_config_d"] = {"rows": n, "ms": ms, "bytes": by, "achieved": by / ms / 1e6,
+                                              "peak": pk["hbm"], "unit": "GB/s", "frac": by / ms / 1e6 / pk["hbm"],
+                                              "note": "38 MB working set: L2-resident between repetitions"}
+    n = full
     return out
 
 
 # ------------------------------------------------------------------------------------------- b200 arm
+def make_trainer(P, torch, dist, wl, n_local, rank, world, args):
+    """one trainer per rank on its env shard; N>1: NCCL communicator (advantage moments) + peer-memory gradient exchange"""
+    tr = P.Trainer(env_kind=wl["env"], obs_dim=wl["O"], hidden=wl["H"], nvec=wl["nvec"], num_envs=n_local,
+                   num_steps=wl["T"], num_minibatches=wl["MB"], update_epochs=wl["E"], max_episode_steps=wl["max_ep"],
+                   seed=2, world_size=world, rank=rank, use_cuda_graph=not args.no_graph, **HYPER)
+    exchange = "none"
+    if world > 1:
+        uid = [P.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        tr.init_comm(uid[0], rank, world)
+        exchange = "nccl"
+        if not args.no_peer:
+            # gradient exchange over peer memory (one fused kernel per rank) instead of reduce -> NCCL -> clip/AdamW
+            hs = [None] * world
+            dist.all_gather_object(hs, tr.peer_handle())
+            try:
+                tr.set_peers(hs)
+                exchange = "peer-memory fused reduce+AdamW (NVLink P2P)"
+            except P.PpoError as e:
+                if rank == 0:
+                    print("peer-memory path unavailable, NCCL path in use:", e, file=sys.stderr)
+    return tr, exchange
+
+
+def time_trainer(torch, dist, tr, K, W, flush, it0_total):
+    """W warm-up iterations, then K device-timed iterations (L2 flushed, untimed, before each) twice: fully asynchronous
+    (value) and through the public call with the host result (e2e).  Returns (ms_dev, ms_e2e, wall_dev), max over ranks."""
+    def lr_at(i):
+        return (1.0 - i / max(1, it0_total)) * LR0        # anneal_lr (PPO_Discrete.cpp:514-518)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_loop(want_result, it0):
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        barrier()
+        for i in range(K):
+            flush.zero_()
+            evs[i][0].record()
+            tr.iterate(lr_at(it0 + i), want_result=want_result)
+            evs[i][1].record()
+        barrier()
+        return sum(s.elapsed_time(e) for s, e in evs)
+
+    for i in range(W):
+        tr.iterate(lr_at(i), want_result=False)
+    barrier()
+    t_wall = time.time()
+    ms_dev = timed_loop(False, W)              # inputs resident in HBM, fully asynchronous iterations
+    wall_dev = time.time() - t_wall
+    ms_e2e = timed_loop(True, W + K)           # public call with host result: scalars H2D, diagnostics D2H, sync
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+    return max_over_ranks(ms_dev), max_over_ranks(ms_e2e), wall_dev
+
+
+UPDATE_PATHS = {0: "fp32 FMA kernels (update_kernel)", 1: "tcgen05, hidden = 64, one fused kernel (update_tc_kernel)",
+                2: "tcgen05, hidden = 256, per-layer pipeline (h256_fwd / h256_dx / h256_dw kernels)"}
+
+
 def run_b200(args, wl_name):
+    import ctypes as C
     import torch
     import ppo_libtorch_b200 as P
     wl = WORKLOADS[wl_name]
@@ -296,77 +407,27 @@ def run_b200(args, wl_name):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pk = peaks()
-
-    tr = P.Trainer(env_kind=wl["env"], obs_dim=wl["O"], hidden=wl["H"], nvec=wl["nvec"], num_envs=wl["N"],
-                   num_steps=wl["T"], num_minibatches=wl["MB"], update_epochs=wl["E"], max_episode_steps=wl["max_ep"],
-                   seed=2, world_size=world, rank=rank, use_cuda_graph=not args.no_graph, **HYPER)
-    if world > 1:
-        uid = [P.unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        tr.init_comm(uid[0], rank, world)
-        if not args.no_peer:
-            # gradient exchange over peer memory (one fused kernel per rank) instead of reduce -> NCCL -> clip/AdamW
-            hs = [None] * world
-            dist.all_gather_object(hs, tr.peer_handle())
-            try:
-                tr.set_peers(hs)
-            except P.PpoError as e:
-                if rank == 0:
-                    print("peer-memory path unavailable, NCCL path in use:", e, file=sys.stderr)
+    total = bool(wl.get("total"))
+    n_local = wl["N"] // world if total else wl["N"]
+    tr, exchange = make_trainer(P, torch, dist, wl, n_local, rank, world, args)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
     K, W = args.steps, args.warmup
-    total_updates = K + W
-
-    def lr_at(i):
-        return (1.0 - i / max(1, 2 * total_updates)) * LR0        # anneal_lr (PPO_Discrete.cpp:514-518)
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed_loop(want_result, it0):
-        """K iterations; L2 flushed (untimed) before each; returns device ms summed over the K steps"""
-        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-        barrier()
-        for i in range(K):
-            flush.zero_()
-            evs[i][0].record()
-            tr.iterate(lr_at(it0 + i), want_result=want_result)
-            evs[i][1].record()
-        barrier()
-        return sum(s.elapsed_time(e) for s, e in evs)
-
-    for i in range(W):
-        tr.iterate(lr_at(i), want_result=False)
-    barrier()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    t_wall = time.time()
-    ms_dev = timed_loop(False, W)              # inputs resident in HBM, fully asynchronous iterations
-    wall_dev = time.time() - t_wall
-    ms_e2e = timed_loop(True, W + K)           # public call with host result: scalars H2D, diagnostics D2H, sync
+    ms_dev, ms_e2e, wall_dev = time_trainer(torch, dist, tr, K, W, flush, 2 * (K + W))
     clk = clocks.stop() if rank == 0 else None
-
-    def max_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return t.item()
-    ms_dev, ms_e2e = max_over_ranks(ms_dev), max_over_ranks(ms_e2e)
-    batch = wl["N"] * wl["T"]
+    batch = n_local * wl["T"]
     total_steps = batch * world * K
     value = total_steps / (ms_dev / 1000.0)
     e2e_value = total_steps / (ms_e2e / 1000.0)
 
     # per-phase device time inside real iterations (cudaEvent pairs on the launch stream, eager launches)
     tr.profile(True)
-    prof_iters = max(1, min(K, 5))
+    prof_iters = max(1, min(K, 3))
     for i in range(prof_iters):
-        tr.iterate(lr_at(i), want_result=False)
+        tr.iterate(LR0 * 0.5, want_result=False)
     phases = tr.phase_ms()
     tr.profile(False)
     n_opt = wl["E"] * wl["MB"]
@@ -378,31 +439,36 @@ def run_b200(args, wl_name):
     achieved_tf = flops_per_launch / (upd_ms_per / 1000.0) / 1e12
     phase_total = sum(v[0] for v in phases.values())
     mode = P.ops.get_math_mode()
-    mode_name = {0: "fp32 FMA path (update_kernel)", 1: "bf16 tcgen05 path (update_tc_kernel)",
-                 2: "fp16 tcgen05 path (update_tc_kernel)"}[mode]
-    roofline = {"bound": "tensor", "kernel": "fused fwd + PPO loss + bwd, " + mode_name,
+    path = int(P.capi.load().ppo_update_path(C.byref(tr.cfg.dims)))     # which kernels serve this shape in this mode
+    traffic = NCU_TRAFFIC.get((wl_name, mode))
+    roofline = {"bound": "tensor", "kernel": "fused fwd + PPO loss + bwd of one minibatch: " + UPDATE_PATHS.get(path, "?"),
                 "achieved": achieved_tf, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
-                "frac": achieved_tf / pk["bf16_sustained"], "traffic": NCU_TRAFFIC.get((wl_name, mode)), "peak_source": pk["source"] +
-                " (bf16 cuBLAS sustained)",
-                "flops_per_launch": flops_per_launch, "ms_per_launch": upd_ms_per,
+                "frac": achieved_tf / pk["bf16_sustained"],
+                "traffic": traffic,
+                "traffic_source": None if traffic is None else
+                "constant from the committed ncu --set full capture named beside NCU_TRAFFIC in bench.py, not re-measured by this run",
+                "peak_source": pk["source"] + " (bf16 cuBLAS sustained)",
+                "flops_per_launch": flops_per_launch, "rows_per_launch": mb_rows, "ms_per_launch": upd_ms_per,
                 "share_of_step": upd_ms / phase_total if phase_total else None}
     # one GPU / peer-memory DP: scalars, rollout, gae, all-epoch advantage statistics, row packing, per minibatch {update,
     # reduce+clip+AdamW}, explained variance.  NCCL DP: per epoch {permutation, moments, finalize}, per minibatch
     # {update, reduce, clip_adamw} (NCCL's own kernels are not counted: not ours).
-    if world == 1 or not args.no_peer:
-        packed = 1 if (wl["H"] == 64 and len(wl["nvec"]) == 1 and wl["O"] <= 4) else 0   # + ppo_pack_rows
-        per_step = 2   # (1 with ppo_debug_fuse_tail(1) when min(tiles, 148) >= (n_par + 63) // 64: measured slower)
-        launches = 4 + packed + 1 + wl["E"] * wl["MB"] * per_step + 1 + (1 if world > 1 else 0)   # + episode tail
+    upd_launches = {0: 1, 1: 1, 2: 6}.get(path, 1)      # kernels per minibatch gradient
+    if world == 1 or exchange.startswith("peer"):
+        packed = 1 if (len(wl["nvec"]) == 1 and wl["O"] <= 4 and wl["H"] in (64, 256)) else 0   # + ppo_pack_rows
+        launches = 4 + packed + 1 + wl["E"] * wl["MB"] * (upd_launches + 1) + 1 + (1 if world > 1 else 0)   # + episode tail
     else:
-        launches = 3 + wl["E"] * (3 + wl["MB"] * 3) + 1
+        launches = 3 + wl["E"] * (3 + wl["MB"] * (upd_launches + 2)) + 1
 
     line = {"metric": "env_steps_per_sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K,
-            "warmup": W, "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": W, "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "strong" if total else "weak",
+            "vs_baseline": None,
             "dtype": {0: "f32", 1: "bf16", 2: "f16"}[mode], "data": "synthetic",
             "config": {"workload": wl_name, "env": "CartPole" if wl["env"] == 0 else "MountainCar",
-                       "envs_per_gpu": wl["N"], "rollout_steps": wl["T"], "hidden": wl["H"], "update_epochs": wl["E"],
-                       "minibatches": wl["MB"], "global_batch": batch * world, "parallelism": f"dp{world}", "grad_exchange": "none" if world == 1 else (
-                           "nccl" if args.no_peer else "peer-memory fused reduce+AdamW (NVLink P2P)"),
+                       "envs_total": n_local * world, "envs_per_gpu": n_local, "rollout_steps": wl["T"],
+                       "hidden": wl["H"], "update_epochs": wl["E"],
+                       "minibatches": wl["MB"], "global_batch": batch * world, "parallelism": f"dp{world}",
+                       "grad_exchange": exchange,
                        "l2": "flushed between steps (256 MiB write, untimed)", "cuda_graph": not args.no_graph,
                        "policy": "orthogonal-init weights, live-sampled actions"},
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": 32,
@@ -410,8 +476,21 @@ def run_b200(args, wl_name):
             "gpu_launches": launches * K, "roofline": roofline,
             "phases_ms_per_step": {k: v[0] / prof_iters for k, v in phases.items()},
             "clocks": clk, "wall_s_timed_region": wall_dev}
+    tr.close()
+    del tr
+    if wl_name != CONFIG_B and not args.no_config_b:
+        # the latency-bound point: BASELINE configs[1], 4096 envs x 128 steps PER GPU (weak), same run, same box
+        wb = WORKLOADS[CONFIG_B]
+        trb, _ = make_trainer(P, torch, dist, wb, wb["N"], rank, world, args)
+        Kb = max(K, 20)
+        mb_dev, mb_e2e, _ = time_trainer(torch, dist, trb, Kb, max(W, 5), flush, 4 * Kb)
+        steps_b = wb["N"] * wb["T"] * world * Kb
+        line["config_b"] = {"workload": CONFIG_B, "scaling": "weak", "envs_per_gpu": wb["N"],
+                            "value": steps_b / (mb_dev / 1000.0), "ms_per_step": mb_dev / Kb,
+                            "e2e_value": steps_b / (mb_e2e / 1000.0), "steps": Kb, "unit": "env-steps/s"}
+        trb.close()
+        del trb
     if rank == 0 and world == 1 and not args.no_kernels:
-        tr.close()
         line["kernels"] = kernel_rooflines(P, torch, pk)
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline_sample(wl_name)
@@ -437,6 +516,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-peer", action="store_true", help="N>1: NCCL gradient allreduce instead of the peer-memory kernel")
     ap.add_argument("--no-kernels", action="store_true", help="skip the stand-alone kernel rooflines")
+    ap.add_argument("--no-config-b", action="store_true", help="skip the extra configs[1] (4096 envs per GPU) measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

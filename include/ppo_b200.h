@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PPO_B200_ABI_VERSION 3
+#define PPO_B200_ABI_VERSION 4
 #define PPO_MAX_HEADS 8
 #define PPO_MAX_LOGITS 64
 
@@ -72,6 +72,9 @@ typedef struct {
 enum { PPO_MATH_FP32 = 0, PPO_MATH_BF16 = 1, PPO_MATH_FP16 = 2 };
 int ppo_set_math_mode(int mode);
 int ppo_get_math_mode(void);
+/* Which kernels serve ppo_update_minibatch / the trainer's update phase for this shape in the current math mode:
+ * 0 = fp32 FMA kernels, 1 = tcgen05 fused kernel (hidden = 64), 2 = tcgen05 per-layer pipeline (hidden = 256). */
+int ppo_update_path(const ppo_dims* dims);
 
 const char* ppo_last_error(void);
 int ppo_abi_version(void);

@@ -38,7 +38,7 @@ class Hyper(C.Structure):
                 ("ent_coef", C.c_float), ("vf_coef", C.c_float), ("entropy_mode", C.c_int32)]
 
 
-ABI_VERSION = 3   # PPO_B200_ABI_VERSION in include/ppo_b200.h (3: episode log fields in ppo_rollout_cfg)
+ABI_VERSION = 4   # PPO_B200_ABI_VERSION in include/ppo_b200.h (4: ppo_update_path, hidden = 256 tensor-core pipeline)
 
 
 class RolloutCfg(C.Structure):
@@ -76,6 +76,7 @@ _PROTOS = {
     "ppo_abi_version": (C.c_int, []),
     "ppo_set_math_mode": (C.c_int, [C.c_int]),
     "ppo_get_math_mode": (C.c_int, []),
+    "ppo_update_path": (C.c_int, [C.POINTER(Dims)]),
     "ppo_adv_stats_all_epochs": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint64,
                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ppo_trainer_peer_handle": (C.c_int, [C.c_void_p, C.c_char_p]),

@@ -2,9 +2,12 @@
 // PPO_MultiDiscrete::train (PPO/PPO_Discrete.cpp:511-673 minus printing and checkpointing) as a
 // stream of kernel launches over one device arena, with no host round trip inside an iteration.
 //
-//   rollout (1 launch) -> GAE (1) -> per epoch { permutation (1), advantage statistics (1),
-//   per minibatch { fused fwd+loss+bwd (2), [gradient allreduce], clip + AdamW (1) } }
-//   -> explained variance (1) -> one D2H of the diagnostics.
+//   iterate():  rollout (1 launch) -> GAE (1) -> advantage statistics of all E x MB minibatches (1; the minibatch
+//   permutation is a keyed bijection evaluated inside the kernels, never materialised) -> row packing (1) ->
+//   per minibatch { fused fwd+loss+bwd (1; 6 at hidden = 256), slab reduction + [NVLink exchange] + clip + AdamW (1) }
+//   -> explained variance (1), episode tail (1) -> one D2H of the diagnostics.
+//   The split-phase API (rollout / begin_epoch / minibatch_grads / apply / finish) and NCCL data parallelism keep the
+//   per-epoch permutation + statistics launches and the separate reduce / allreduce / clip + AdamW launches.
 //
 // With use_cuda_graph the whole iteration is captured once and replayed; the values that change
 // between iterations (learning rate, optimiser step, RNG counters) live in device scalars.
@@ -440,7 +443,7 @@ static int phase_minibatch_step(ppo_trainer* t, int epoch, int mb, cudaStream_t 
     f.beta1 = c.beta1; f.beta2 = c.beta2; f.eps = c.adam_eps; f.weight_decay = c.weight_decay;
     f.step_host = (int64_t)k + 1; f.d_step = &t->d_scal->step_base; f.max_grad_norm = c.max_grad_norm;
     f.norm_out = t->norm_out; f.diag_hist = t->diag_hist + (size_t)k * 8;
-    const bool peer = c.world_size > 1;   // caller checked peer_ready
+    const bool peer = c.world_size > 1 && t->peer_ready;   // enqueue_iteration only takes this path with peers mapped
     ppo::PermFn pf{};
     pf.inline_on = 1; pf.half_bits = ppo::perm_half_bits(t->B); pf.batch = t->B; pf.seed = perm_seed(c);
     pf.epoch = (uint64_t)epoch; pf.d_epoch = &t->d_scal->epoch_counter;
@@ -491,6 +494,10 @@ static int enqueue_iteration(ppo_trainer* t, cudaStream_t st) {
     t->opt_in_iter = 0;
     if ((rc = phase_rollout(t, st))) return rc;
     const bool dp = t->cfg.world_size > 1 && t->comm;
+    // world_size > 1 needs a transport: the NCCL communicator (advantage moments, and gradients without peer memory)
+    PPO_REQUIRE(t->cfg.world_size == 1 || t->comm,
+                "world_size = %d but no communicator: call ppo_trainer_set_comm (and optionally ppo_trainer_set_peers) first",
+                t->cfg.world_size);
     const bool fused = (!dp || t->peer_ready) && !t->profile;
     if (fused) {   // no per-epoch launches: statistics of every epoch up front, permutation evaluated inside the update kernel
         if ((rc = phase_all_epoch_stats(t, st))) return rc;

@@ -530,6 +530,16 @@ extern "C" int64_t ppo_update_workspace_bytes(const ppo_dims* dims) {
            upd_tail_bytes(P);
 }
 
+// which kernels serve ppo_update_minibatch for this shape in the current math mode (bench.py labels its roofline with it)
+extern "C" int ppo_update_path(const ppo_dims* dims) {
+    Dims d;
+    if (make_dims(dims, &d)) return -1;
+    if (math_mode() == PPO_MATH_FP32) return 0;
+    if (update_tc_supported(d)) return 1;
+    if (update_h256_supported(d)) return 2;
+    return 0;
+}
+
 extern "C" int ppo_update_minibatch(const float* params, const ppo_dims* dims, const float* obs, const uint8_t* mask,
                                     const int32_t* actions, const float* old_logprob, const float* adv,
                                     const float* ret, const float* old_val, const int32_t* perm, int64_t mb_start,

@@ -95,4 +95,7 @@ int update_minibatch_fused(const float* params, const ppo_dims* dims, const floa
 int launch_update_tc(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st, const FuseAdam* fuse = nullptr,
                      float* grads_out = nullptr, float* diag_out = nullptr, bool* tail_done = nullptr);
 
+bool update_tc_supported(const Dims& d);     // update_tc.cu: hidden = 64 envelope
+bool update_h256_supported(const Dims& d);   // update_h256.cu: hidden = 256 envelope
+
 }  // namespace ppo

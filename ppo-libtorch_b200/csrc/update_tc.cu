@@ -998,11 +998,13 @@ extern "C" int ppo_debug_tc_timeline(long long* d_ts, int who) {
     return PPO_OK;
 }
 namespace ppo {
+bool update_tc_supported(const Dims& d) {
+    return d.H == TC_H && d.O + 1 <= 8 && d.K <= TC_MAX_K && (size_t)tc_layout(d.K, 2).end + 1024 <= 227 * 1024;
+}
 int launch_update_tc(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st, const FuseAdam* fuse, float* grads_out,
                      float* diag_out, bool* tail_done) {
     if (tail_done) *tail_done = false;
-    if (a.d.H != TC_H || a.d.O + 1 > 8 || a.d.K > TC_MAX_K) return PPO_ERR_UNSUPPORTED;
-    if ((size_t)tc_layout(a.d.K, 2).end + 1024 > 227 * 1024) return PPO_ERR_UNSUPPORTED;
+    if (!update_tc_supported(a.d)) return PPO_ERR_UNSUPPORTED;
     const bool wide = a.d.O + 1 > 4;
     if (fmt == FMT_BF16)
         return wide ? launch_tc<FMT_BF16, 2, true>(a, grid_out, st, fuse, grads_out, diag_out, tail_done)

@@ -28,7 +28,7 @@ def num_params(obs_dim, hidden, nvec):
 
 
 def set_math_mode(mode):
-    """capi.MATH_FP32 (FMA kernels, oracle-exact to 1e-4) / MATH_BF16 (default) / MATH_FP16 (tcgen05 tensor cores);
+    """capi.MATH_FP32 (FMA kernels, oracle-exact to 1e-4) / MATH_FP16 (default) / MATH_BF16 (tcgen05 tensor cores);
     the reference's counterpart is at::globalContext().setAllowTF32CuBLAS (PPO/PPO_Discrete.cpp:56)."""
     check(load().ppo_set_math_mode(int(mode)))
 
@@ -192,6 +192,13 @@ def adv_stats_finalize(partials):
 
 
 _ws_cache = {}
+
+
+def update_path(obs_dim, hidden, nvec):
+    """0 = fp32 FMA kernels, 1 = tcgen05 fused kernel (hidden 64), 2 = tcgen05 per-layer pipeline (hidden 256), for this
+    shape in the current math mode (ppo_update_path)"""
+    d = Dims.make(obs_dim, hidden, nvec)
+    return int(load().ppo_update_path(C.byref(d)))
 
 
 def update_minibatch(params, obs_dim, hidden, nvec, obs, actions, old_logprob, adv, ret, old_val, mb_start, mb_size,

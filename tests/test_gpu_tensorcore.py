@@ -1,6 +1,7 @@
-"""GPU tests of the tcgen05 (TF32 operands, fp32 TMEM accumulators) path: first the building blocks
-(csrc/umma.cuh through ppo_debug_umma_probe) against a numpy TF32 model, then the tensor-core update kernel
-against the oracle within the stated TF32 tolerance."""
+"""GPU tests of the tcgen05 path (fp16 / bf16 operands, fp32 accumulators in tensor memory): first the building blocks
+(csrc/umma.cuh through ppo_debug_umma_probe) against a numpy model of 16-bit operands, then the tensor-core update kernels
+(hidden = 64: one fused kernel; hidden = 256: per-layer pipeline) against the oracle within the stated tolerance, then
+the trainer in its DEFAULT arithmetic mode (fp16 operands): learning curve, config-B-sized run against the fp32 path."""
 import ctypes as C
 
 import numpy as np
@@ -79,9 +80,9 @@ def math_mode(P):
     P.ops.set_math_mode(prev)
 
 
-def _make_case(P, orc, O, nvec, batch, masked, seed):
+def _make_case(P, orc, O, nvec, batch, masked, seed, H=64):
     rng = np.random.default_rng(seed)
-    K, heads, H = sum(nvec), len(nvec), 64
+    K, heads = sum(nvec), len(nvec)
     params = P.orthogonal_init_params(O, H, nvec, seed=5)
     params += rng.standard_normal(params.size).astype(np.float32) * 0.05
     obs = rng.standard_normal((batch, O)).astype(np.float32)
@@ -119,46 +120,88 @@ GTOL_CLIP = {1: 1.0e-1, 2: 1.5e-2}
 LTOL = {1: 1e-2, 2: 2e-3}
 
 
-def _net_errors(g, og, O, K):
-    ncrit = 64 * O + 64 + 64 * 64 + 64 + 64 + 1
+def _net_errors(g, og, O, K, H=64):
+    """relative L2 gradient error per net (critic slab, actor slab).  A net whose oracle gradient is exactly zero (the
+    single-logit actor: softmax over one logit is constant) must be exactly zero here too and reports 0."""
+    ncrit = H * O + H + H * H + H + H + 1
     out = []
     for sl in (slice(0, ncrit), slice(ncrit, None)):
-        out.append(np.linalg.norm(g[sl] - og[sl]) / np.linalg.norm(og[sl]))
+        den = np.linalg.norm(og[sl])
+        if den == 0.0:
+            assert not np.any(g[sl]), "oracle gradient of this net is exactly zero; the kernel's is not"
+            out.append(0.0)
+        else:
+            out.append(np.linalg.norm(g[sl] - og[sl]) / den)
     return out
 
 
+def _oracle_grads(orc, c, H, O, nvec, rows, emode, hyp, threads=1):
+    """oracle gradient of the minibatch `rows`.  threads > 1: the rows are cut into chunks evaluated concurrently (the C
+    oracle is single-threaded and releases the GIL under ctypes); advantages are normalised up front with the minibatch
+    statistics (fp32, like PPO_Discrete.cpp:591-594) and chunk gradients / diagnostics are combined with weights n_c / n."""
+    mask = None if c["mask"] is None else c["mask"][rows]
+    kw = dict(ent_coef=0.01, entropy_mode=emode, **hyp)
+    if threads <= 1:
+        return orc.minibatch_grads(c["params"], O, H, np.array(nvec, np.int32), c["obs"][rows], c["acts"][rows],
+                                   c["old_lp"][rows], c["adv"][rows], c["ret"][rows], c["old_val"][rows], mask=mask, **kw)
+    from concurrent.futures import ThreadPoolExecutor
+    adv = c["adv"][rows].astype(np.float32)
+    mean = np.float32(adv.astype(np.float64).mean())
+    std = np.float32(adv.astype(np.float64).std(ddof=1))
+    advn = ((adv - mean) / (std + np.float32(1e-8))).astype(np.float32)
+    n = len(rows)
+    cuts = np.linspace(0, n, threads * 4 + 1).astype(np.int64)
+
+    def one(i):
+        sl = slice(cuts[i], cuts[i + 1])
+        r = rows[sl]
+        g, d = orc.minibatch_grads(c["params"], O, H, np.array(nvec, np.int32), c["obs"][r], c["acts"][r], c["old_lp"][r],
+                                   advn[sl], c["ret"][r], c["old_val"][r], mask=None if mask is None else mask[sl],
+                                   norm_adv=False, **kw)
+        w = (cuts[i + 1] - cuts[i]) / n
+        return g.astype(np.float64) * w, d.astype(np.float64) * w
+    with ThreadPoolExecutor(threads) as ex:
+        parts = list(ex.map(one, range(len(cuts) - 1)))
+    return sum(p[0] for p in parts), sum(p[1] for p in parts)
+
+
+# (H, O, nvec, n, masked, exact).  hidden = 64: the fused kernel (update_tc.cu); hidden = 256: the per-layer pipeline
+# (update_h256.cu: forward / dX / dW kernels), incl. ragged row counts (n % 128 != 0), n < 128 and a masked two-head case.
+TC_CASES = [(64, 4, [2], 1000, False, False), (64, 4, [2], 131072, False, False), (64, 2, [3], 4099, True, False),
+            (64, 4, [1], 65, False, False), (64, 4, [3, 3, 3, 3, 3, 2, 2, 2], 777, True, True),
+            (64, 7, [5, 4], 300, False, True),
+            (256, 2, [3], 4099, False, False), (256, 4, [2], 1000, False, True), (256, 2, [3], 65, False, False),
+            (256, 2, [3], 131072, False, False), (256, 4, [3, 2], 777, True, True), (256, 2, [1], 300, False, False)]
+
+
 @pytest.mark.parametrize("mode", [1, 2])
-@pytest.mark.parametrize("O,nvec,n,masked,exact", [(4, [2], 1000, False, False), (4, [2], 131072, False, False),
-                                                   (2, [3], 4099, True, False), (4, [1], 65, False, False),
-                                                   (4, [3, 3, 3, 3, 3, 2, 2, 2], 777, True, True),
-                                                   (7, [5, 4], 300, False, True)])
+@pytest.mark.parametrize("H,O,nvec,n,masked,exact", TC_CASES,
+                         ids=[f"h{c[0]}-o{c[1]}-nvec{'x'.join(map(str, c[2]))}-n{c[3]}-m{int(c[4])}-e{int(c[5])}" for c in TC_CASES])
 @pytest.mark.parametrize("smooth", [False, True])
-def test_update_tc_vs_oracle(P, orc, math_mode, mode, O, nvec, n, masked, exact, smooth):
+def test_update_tc_vs_oracle(P, orc, math_mode, mode, H, O, nvec, n, masked, exact, smooth):
     batch = n + 300
-    c = _make_case(P, orc, O, nvec, batch, masked, seed=n + mode)
+    c = _make_case(P, orc, O, nvec, batch, masked, seed=n + mode, H=H)
     start = 5
     rows = c["perm"][start:start + n]
     emode = P.ENTROPY_EXACT if exact else P.ENTROPY_REFERENCE
     dperm = dev(c["perm"])
     stat = P.ops.adv_stats(dev(c["adv"]), n, 1, perm=dperm[start:start + n].contiguous())
-    args = (dev(c["params"]), O, 64, nvec, dev(c["obs"]), dev(c["acts"]), dev(c["old_lp"]), dev(c["adv"]),
+    args = (dev(c["params"]), O, H, nvec, dev(c["obs"]), dev(c["acts"]), dev(c["old_lp"]), dev(c["adv"]),
             dev(c["ret"]), dev(c["old_val"]), start, n)
     # smooth: thresholds out of reach (clip_coef 10, no value clipping) so that only rounding separates the two
     hyp = dict(clip_coef=10.0, clip_vloss=False) if smooth else dict(clip_coef=0.2, clip_vloss=True)
     kw = dict(perm=dperm, mask=None if c["mask"] is None else dev(c["mask"]), adv_stat=stat, ent_coef=0.01,
               entropy_mode=emode, **hyp)
     math_mode(mode)
+    assert P.ops.update_path(O, H, nvec) == (1 if H == 64 else 2), "the tensor-core kernels must serve this shape"
     grads, diag = P.ops.update_minibatch(*args, **kw)
     grads2, diag2 = P.ops.update_minibatch(*args, **kw)
     torch.cuda.synchronize()
-    og, od = orc.minibatch_grads(c["params"], O, 64, np.array(nvec, np.int32), c["obs"][rows], c["acts"][rows],
-                                 c["old_lp"][rows], c["adv"][rows], c["ret"][rows], c["old_val"][rows],
-                                 mask=None if c["mask"] is None else c["mask"][rows], ent_coef=0.01, entropy_mode=emode,
-                                 **hyp)
+    og, od = _oracle_grads(orc, c, H, O, nvec, rows, emode, hyp, threads=8 if n * H >= 1 << 22 else 1)
     g = grads.cpu().numpy().astype(np.float64)
     assert np.isfinite(g).all()
     gtol = (GTOL_SMOOTH if smooth else GTOL_CLIP)[mode]
-    errs = _net_errors(g, og, O, sum(nvec))
+    errs = _net_errors(g, og, O, sum(nvec), H)
     assert max(errs) < gtol, f"relative L2 gradient error critic/actor {errs} exceeds {gtol}"
     d = diag.cpu().numpy()
     np.testing.assert_allclose(d[:5], od[:5], rtol=LTOL[mode], atol=LTOL[mode] * 1e-2)
@@ -166,6 +209,70 @@ def test_update_tc_vs_oracle(P, orc, math_mode, mode, O, nvec, n, masked, exact,
     # deterministic run to run (fixed-order slab reduction, in-order tensor-memory accumulation)
     assert torch.equal(grads, grads2) and torch.equal(diag, diag2)
     # and the fp32 FMA kernels still serve the same call
-    math_mode(0)
-    g32, _ = P.ops.update_minibatch(*args, **kw)
-    np.testing.assert_allclose(g32.cpu().numpy(), og, rtol=1e-4, atol=3e-6 * np.abs(og).max())
+    if n * H <= 1 << 22:
+        math_mode(0)
+        g32, _ = P.ops.update_minibatch(*args, **kw)
+        np.testing.assert_allclose(g32.cpu().numpy(), og, rtol=1e-4, atol=3e-6 * np.abs(og).max())
+
+
+def test_update_tc_config_e_shard_rows(P, orc, math_mode):
+    """4 194 304 rows in ONE launch (the minibatch of a 131 072-env x 128-step shard, BASELINE configs[4] at 8 GPUs): the
+    un-normalised weight-gradient accumulators (1/n is applied at the drain) are at their largest here; they live in fp32
+    tensor memory and the fp16 operand tiles are per-row quantities, so nothing leaves fp16 range."""
+    O, nvec, H, n = 4, [2], 64, 4194304
+    c = _make_case(P, orc, O, nvec, n, False, seed=77, H=H)
+    rows = c["perm"]
+    hyp = dict(clip_coef=0.2, clip_vloss=True)
+    dperm = dev(c["perm"])
+    stat = P.ops.adv_stats(dev(c["adv"]), n, 1, perm=dperm)
+    math_mode(2)
+    grads, diag = P.ops.update_minibatch(dev(c["params"]), O, H, nvec, dev(c["obs"]), dev(c["acts"]), dev(c["old_lp"]),
+                                         dev(c["adv"]), dev(c["ret"]), dev(c["old_val"]), 0, n, perm=dperm, adv_stat=stat,
+                                         ent_coef=0.01, entropy_mode=P.ENTROPY_REFERENCE, **hyp)
+    torch.cuda.synchronize()
+    og, od = _oracle_grads(orc, c, H, O, nvec, rows, P.ENTROPY_REFERENCE, hyp, threads=16)
+    g = grads.cpu().numpy().astype(np.float64)
+    assert np.isfinite(g).all()
+    errs = _net_errors(g, og, O, 2, H)
+    assert max(errs) < GTOL_CLIP[2], f"relative L2 gradient error critic/actor {errs}"
+    np.testing.assert_allclose(diag.cpu().numpy()[:5], od[:5], rtol=LTOL[2], atol=LTOL[2] * 1e-2)
+
+
+# ------------------------------------------------------------------------------- the trainer in its default mode
+def _run_trainer(P, mode, iters, **kw):
+    prev = P.ops.get_math_mode()
+    P.ops.set_math_mode(mode)
+    try:
+        tr = P.Trainer(nvec=(2,), seed=2, **kw)
+        curve = []
+        for it in range(iters):
+            r = tr.iterate((1.0 - it / iters) * 1e-3)
+            assert np.isfinite(r["loss"]) and np.isfinite(r["grad_norm"])
+            curve.append(r["ep_len_sum"] / max(r["episodes"], 1.0))
+        tr.close()
+        return np.array(curve)
+    finally:
+        P.ops.set_math_mode(prev)
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_trainer_learns_cartpole_default_mode(P, graph):
+    """the learning-curve acceptance of tests/test_gpu_parity.py::test_trainer_learns_cartpole, in the DEFAULT arithmetic
+    (fp16 tcgen05 update kernel; at 64 envs the rollout is the fp32 FMA kernel)"""
+    assert P.ops.get_math_mode() == P.capi.MATH_FP16, "fp16 operands are the library default"
+    curve = _run_trainer(P, P.capi.MATH_FP16, 60, num_envs=64, num_steps=32, num_minibatches=4, update_epochs=10,
+                         use_cuda_graph=graph)
+    assert curve[0] < 40
+    assert curve[-1] > 100, f"mean episode length only reached {curve[-1]}"
+
+
+def test_trainer_config_b_default_mode_tracks_fp32(P):
+    """BASELINE configs[1] (4096 envs x 128 steps, the shape bench.py's config_b times) for 15 iterations from one seed in
+    the default fp16 mode and on the fp32 FMA kernels.  The two runs diverge sample by sample (a sampled action flips as
+    soon as a probability differs in the last bits), so the comparison is statistical: mean episode length of every
+    iteration within 15 % + 2 steps of the fp32 run's, and both learn."""
+    kw = dict(num_envs=4096, num_steps=128, num_minibatches=4, update_epochs=10, use_cuda_graph=True)
+    c16 = _run_trainer(P, P.capi.MATH_FP16, 15, **kw)
+    c32 = _run_trainer(P, P.capi.MATH_FP32, 15, **kw)
+    assert c32[-1] > 2.0 * c32[0] and c16[-1] > 2.0 * c16[0], f"fp32 {c32}, fp16 {c16}"
+    assert np.all(np.abs(c16 - c32) <= 0.15 * c32 + 2.0), f"fp16 {c16}\nfp32 {c32}"
