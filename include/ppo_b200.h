@@ -76,6 +76,11 @@ int ppo_get_math_mode(void);
  * 0 = fp32 FMA kernels, 1 = tcgen05 fused kernel (hidden = 64), 2 = tcgen05 per-layer pipeline (hidden = 256). */
 int ppo_update_path(const ppo_dims* dims);
 
+/* Upper bound (milliseconds of SM clock, 0 = default ~20 s) of every in-kernel wait on another CTA or another rank.  A
+ * wait that runs out sets the trainer's sticky error flag and SKIPS the optimiser step on that rank; the next
+ * synchronised ppo_trainer_iterate returns PPO_ERR_COMM. */
+int ppo_set_spin_timeout_ms(int64_t ms);
+
 const char* ppo_last_error(void);
 int ppo_abi_version(void);
 /* number of visible CUDA devices (0 => nothing below can run) */

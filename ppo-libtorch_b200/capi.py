@@ -84,6 +84,7 @@ _PROTOS = {
     "ppo_debug_rollout_impl": (C.c_int, [C.c_int]),
     "ppo_debug_pack_rows": (C.c_int, [C.c_int]),
     "ppo_debug_pdl": (C.c_int, [C.c_int]),
+    "ppo_set_spin_timeout_ms": (C.c_int, [C.c_int64]),
     "ppo_debug_fuse_tail": (C.c_int, [C.c_int]),
     "ppo_trainer_last_episodes": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "ppo_episode_tail": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int] + [C.c_void_p] * 4),
@@ -159,8 +160,8 @@ def load():
         for name, (res, args) in _PROTOS.items():
             fn = getattr(lib, name)      # AttributeError if the symbol is not exported
             fn.restype, fn.argtypes = res, args
-        if os.environ.get("PPO_B200_PDL") == "0":   # A/B switch for benchmarks (programmatic dependent launch off)
-            lib.ppo_debug_pdl(0)
+        if os.environ.get("PPO_B200_PDL") is not None:   # A/B switch for benchmarks: bit 0 = single-GPU chain, bit 1 = peer chain
+            lib.ppo_debug_pdl(int(os.environ["PPO_B200_PDL"]))
         _lib = lib
     return _lib
 

@@ -69,10 +69,19 @@ extern "C" const char* ppo_last_error(void) { return g_err; }
 extern "C" int ppo_abi_version(void) { return PPO_B200_ABI_VERSION; }
 
 namespace ppo {
-int g_pdl = 1;
+int g_pdl = 1;              // bit 0: programmatic dependent launch on the single-GPU minibatch chain, bit 1: on the peer chain
+long long g_spin_cycles = 0;   // 0 = the kernels' default (4e10 cycles, ~20 s)
 }
 extern "C" int ppo_debug_pdl(int on) {
     ppo::g_pdl = on;
+    return PPO_OK;
+}
+// Upper bound of every in-kernel wait for another CTA / another rank (gradient exchange over peer memory, grid tickets).
+// A wait that runs out sets the trainer's error flag, SKIPS the optimiser step (no rank steps on a partial gradient sum)
+// and the next synchronised ppo_trainer_iterate returns PPO_ERR_COMM.
+extern "C" int ppo_set_spin_timeout_ms(int64_t ms) {
+    PPO_REQUIRE(ms >= 0, "ppo_set_spin_timeout_ms: negative");
+    ppo::g_spin_cycles = ms * 1965000ll;   // SM clock ceiling of B200 (1 965 MHz)
     return PPO_OK;
 }
 extern "C" int ppo_get_math_mode(void) { return g_math_mode; }

@@ -152,6 +152,7 @@ static inline cudaStream_t as_stream(ppo_stream_t s) { return reinterpret_cast<c
 // and its memory is visible).  pdl_trigger() in the predecessor lets the successor's launch proceed early.  Both are no-ops
 // for a kernel launched the ordinary way.  Captured into CUDA graphs as programmatic edges.
 extern int g_pdl;   // ppo_debug_pdl
+extern long long g_spin_cycles;   // ppo_set_spin_timeout_ms
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 template <class... KArgs, class... Args>
@@ -161,7 +162,7 @@ static inline cudaError_t launch_pdl(bool allow, void (*kernel)(KArgs...), dim3 
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = (g_pdl && allow) ? 1 : 0;
+    attr[0].val.programmaticStreamSerializationAllowed = allow ? 1 : 0;
     cfg.attrs = attr; cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }

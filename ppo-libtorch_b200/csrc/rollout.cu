@@ -449,6 +449,7 @@ static int launch_rollout64(const RollArgs& a, cudaStream_t st) {
 }
 
 static int g_rollout_impl = 1;   // 0 = generic kernel for every shape (ppo_debug_rollout_impl)
+static int g_rollout_h256_min = 1024;  // 128-env MMA tiles: below ~8 tiles the 32-env FMA tiles spread over more SMs
 static int g_rollout_tc_min = 8192;   // below ~8k envs a step is latency-bound and the FMA tiles (16 envs per CTA) win
 
 template <class Env>
@@ -463,6 +464,10 @@ static int dispatch_rollout(const RollArgs& a, cudaStream_t st) {
         if (a.cfg.n_envs <= 32 * sms) return launch_rollout64<Env, 16>(a, st);
         return launch_rollout64<Env, 32>(a, st);
     }
+    // hidden = 256 in the 16-bit modes: layer 2 on the tensor core (rollout_h256.cu); PPO_MATH_FP32 keeps the FMA tiles
+    if (rollout_h256_supported(a.d) && math_mode() != PPO_MATH_FP32 &&
+        (g_rollout_impl == 3 || (g_rollout_impl == 1 && a.cfg.n_envs >= g_rollout_h256_min)))
+        return launch_rollout_h256<Env>(a, math_mode() == PPO_MATH_BF16 ? 1 : 0, st);
     switch (a.d.H) {
         case 64: return launch_rollout<Env, 32, 64>(a, st);
         case 128: return launch_rollout<Env, 32, 128>(a, st);

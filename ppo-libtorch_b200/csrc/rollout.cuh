@@ -29,4 +29,12 @@ template <class Env>
 int launch_rollout_tc(const RollArgs& a, cudaStream_t st);
 bool rollout_tc_supported(const Dims& d);
 
+// rollout_h256.cu: H = 256 in the 16-bit arithmetic modes: actor-only rollout kernel with W2 resident + one batched critic
+// pass for m_values / next_value (fmt: umma::FMT_F16 / FMT_BF16)
+template <class Env>
+int launch_rollout_h256(const RollArgs& a, int fmt, cudaStream_t st);
+bool rollout_h256_supported(const Dims& d);
+int launch_value_h256(const float* params, const Dims& d, const float* obs_a, float* out_a, int64_t rows_a,
+                      const float* soa_b, float* out_b, int rows_b, int fmt, cudaStream_t st);
+
 }  // namespace ppo

@@ -92,6 +92,7 @@ struct ppo_trainer {
     int opt_in_iter = 0;  // optimiser steps issued in the current iteration (split-phase API)
     // peer-memory gradient exchange (update.cuh: PeerArgs): own exchange buffer + the peers' IPC mappings
     char* xchg = nullptr;
+    unsigned* err_flag = nullptr;   // device word: an in-kernel wait (grid ticket, peer exchange) ran out; sticky
     ppo::PeerArgs peer{};
     bool peer_ready = false;
     // optional per-phase device timing (cudaEvent pairs on the launch stream; eager mode only)
@@ -209,7 +210,8 @@ extern "C" ppo_trainer* ppo_trainer_create(const ppo_trainer_cfg* c) {
         {"fin_len", (void**)&t->fin_len, (size_t)T * N * 4},
         {"fin_ret", (void**)&t->fin_ret, (size_t)T * N * 4},
         {"tail", (void**)&t->tail, (size_t)(2 + 2 * PPO_EPISODE_TAIL) * 4},
-        {"rec", (void**)&t->rec, (heads == 1 && !masked && O <= 4 && t->d.H == 64) ? (size_t)t->B * 64 : 0},
+        {"err_flag", (void**)&t->err_flag, 16},
+        {"rec", (void**)&t->rec, (heads == 1 && !masked && O <= 4 && (t->d.H == 64 || t->d.H == 256)) ? (size_t)t->B * 64 : 0},
     };
     size_t total = 0;
     for (auto& it : items) total += al256(it.bytes);
@@ -233,12 +235,18 @@ extern "C" ppo_trainer* ppo_trainer_create(const ppo_trainer_cfg* c) {
         ppo_trainer_destroy(t);
         return nullptr;
     }
+    // hidden = 256 tensor-core update path: its 16-bit activation scratch (h1, dZ2 of one minibatch) is allocated here,
+    // outside any stream capture
+    if (c->update_epochs > 0 && ppo::update_h256_supported(t->d) && ppo::h256_reserve(t->mb_size) != PPO_OK) {
+        ppo_trainer_destroy(t);
+        return nullptr;
+    }
     cudaDeviceSynchronize();
     return t;
 }
 
 // ---- peer-memory gradient exchange: CUDA IPC plumbing ---------------------------------------------------------------
-static size_t xchg_bytes(const ppo_trainer* t) { return 2 * (size_t)ppo::peer_slot_bytes(t->P) + 256; }
+static size_t xchg_bytes(const ppo_trainer* t) { return 2 * (size_t)ppo::peer_slot_bytes(t->P, t->cfg.world_size) + 256; }
 
 extern "C" int ppo_trainer_peer_handle(ppo_trainer* t, char* h_handle64) {
     PPO_REQUIRE(t && h_handle64, "ppo_trainer_peer_handle: null argument");
@@ -276,7 +284,7 @@ extern "C" int ppo_trainer_set_peers(ppo_trainer* t, const char* h_handles, int 
         PPO_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
         t->peer.xchg[r] = (char*)p;
     }
-    t->peer.err = reinterpret_cast<unsigned*>(t->xchg + 2 * (size_t)ppo::peer_slot_bytes(t->P));
+    t->peer.err = t->err_flag;
     t->peer_ready = true;
     if (t->graph_exec) { cudaGraphExecDestroy(t->graph_exec); t->graph_exec = nullptr; }
     return PPO_OK;
@@ -318,6 +326,13 @@ extern "C" int ppo_trainer_set_opt_state(ppo_trainer* t, const float* m, const f
     PPO_REQUIRE(t && step >= 0, "bad argument");
     if (m) PPO_CUDA(cudaMemcpy(t->exp_avg, m, (size_t)t->P * 4, cudaMemcpyHostToDevice));
     if (v) PPO_CUDA(cudaMemcpy(t->exp_avg_sq, v, (size_t)t->P * 4, cudaMemcpyHostToDevice));
+    if (t->xchg && step != t->step) {
+        // flags in the exchange buffer are step numbers: after a jump of the step counter stale ones could satisfy a wait
+        // (or block one).  Every rank calls this collectively and synchronises (host barrier) before the next iterate.
+        PPO_CUDA(cudaDeviceSynchronize());
+        PPO_CUDA(cudaMemset(t->xchg, 0, xchg_bytes(t)));
+        PPO_CUDA(cudaDeviceSynchronize());
+    }
     t->step = step;
     return PPO_OK;
 }
@@ -443,6 +458,8 @@ static int phase_minibatch_step(ppo_trainer* t, int epoch, int mb, cudaStream_t 
     f.beta1 = c.beta1; f.beta2 = c.beta2; f.eps = c.adam_eps; f.weight_decay = c.weight_decay;
     f.step_host = (int64_t)k + 1; f.d_step = &t->d_scal->step_base; f.max_grad_norm = c.max_grad_norm;
     f.norm_out = t->norm_out; f.diag_hist = t->diag_hist + (size_t)k * 8;
+    f.err = t->err_flag; f.spin_cycles = ppo::g_spin_cycles;
+    t->peer.spin_cycles = ppo::g_spin_cycles;
     const bool peer = c.world_size > 1 && t->peer_ready;   // enqueue_iteration only takes this path with peers mapped
     ppo::PermFn pf{};
     pf.inline_on = 1; pf.half_bits = ppo::perm_half_bits(t->B); pf.batch = t->B; pf.seed = perm_seed(c);
@@ -485,7 +502,7 @@ static int phase_tail(ppo_trainer* t, cudaStream_t st) {
                   "Readback tail block mirrors the device tail buffer");
     PPO_CUDA(cudaMemcpyAsync(&t->h_rb->tail_count, t->tail, (size_t)(2 + 2 * PPO_EPISODE_TAIL) * 4,
                              cudaMemcpyDeviceToHost, st));
-    if (t->peer_ready) PPO_CUDA(cudaMemcpyAsync(&t->h_rb->peer_err, t->peer.err, 4, cudaMemcpyDeviceToHost, st));
+    PPO_CUDA(cudaMemcpyAsync(&t->h_rb->peer_err, t->err_flag, 4, cudaMemcpyDeviceToHost, st));
     return PPO_OK;
 }
 
@@ -582,8 +599,9 @@ extern "C" int ppo_trainer_iterate(ppo_trainer* t, float h_lr, ppo_iter_result* 
     if (h_result) {
         PPO_CUDA(cudaStreamSynchronize(st));
         fill_result(t, h_lr, h_result);
-        if (t->peer_ready && t->h_rb->peer_err) {
-            set_error("peer-memory gradient exchange: a rank did not publish its gradient block within the spin limit");
+        if (t->h_rb->peer_err) {
+            set_error("an in-kernel wait ran out (%s): the optimiser steps from there on were skipped",
+                      t->peer_ready ? "a rank did not publish its gradient block within the spin limit" : "grid ticket");
             return PPO_ERR_COMM;
         }
     }

@@ -175,6 +175,7 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_apply_kernel(
     __shared__ double part[RED_PARTS][RED_COLS];
     __shared__ double shn[RED_COLS * RED_PARTS / 32];
     __shared__ unsigned s_last;
+    if (threadIdx.x == 0) s_last = 0u;
     const int col = threadIdx.x & (RED_COLS - 1), pt = threadIdx.x / RED_COLS;
     const int i = blockIdx.x * RED_COLS + col;
     pdl_trigger();   // the next update kernel may be scheduled behind this grid; it waits for our completion itself
@@ -237,14 +238,17 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_apply_kernel(
             sq_part[blockIdx.x] = shn[0] + shn[1];
             __threadfence();
             atomicAdd(ticket, 1u);
-            const long long t0 = clock64();   // bounded: a CTA that never sees the others falls through (no GPU hang)
+            const long long t0 = clock64();   // bounded: a CTA that never sees the others gives up (no GPU hang) ...
+            const long long lim = f.spin_cycles > 0 ? f.spin_cycles : 40000000000ll;
             while (*reinterpret_cast<volatile unsigned*>(ticket) < gridDim.x) {
-                if (clock64() - t0 > 4000000000ll) break;
+                if (clock64() - t0 > lim) { if (f.err) atomicExch(f.err, 1u); s_last = 2u; break; }
                 __nanosleep(32);
             }
             __threadfence();
         }
         __syncthreads();
+        // ... and does NOT step: a partial norm would clip with the wrong coefficient (the host sees PPO_ERR_COMM)
+        if (s_last == 2u || (f.err && *reinterpret_cast<volatile unsigned*>(f.err))) return;
         j0 = blockIdx.x * RED_COLS;
         j1 = min(P, j0 + RED_COLS);
     } else {
@@ -327,6 +331,9 @@ __device__ __forceinline__ float ld_sys_f32(const float* p) {
 __device__ __forceinline__ void st_sys_u32(unsigned* p, unsigned v) {
     asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void st_sys_f32(float* p, float v) {
+    asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
 __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel(
     const float* __restrict__ slabs, const double* __restrict__ dpart, int nslabs, int P, int64_t stride, float inv_n,
     float ent_coef, float vf_coef, float* grads_out, float* __restrict__ diag_out, const FuseAdam f,
@@ -334,14 +341,16 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel
     unsigned* ticket, double* sq_part) {
     __shared__ double part[RED_PARTS][RED_COLS];
     __shared__ double shn[RED_COLS * RED_PARTS / 32];
+    __shared__ unsigned s_fail;
     const int col = threadIdx.x & (RED_COLS - 1), pt = threadIdx.x / RED_COLS;
     const int i = blockIdx.x * RED_COLS + col;
     const int64_t step = f.step_host + (f.d_step ? *f.d_step : 0);
     const unsigned seq = (unsigned)step;
     const int64_t px = peer_px(P);
-    const int64_t slot_off = (int64_t)(seq & 1u) * peer_slot_bytes(P);
-    float* my_data = reinterpret_cast<float*>(pa.xchg[pa.rank] + slot_off);
-    unsigned* my_flags = reinterpret_cast<unsigned*>(pa.xchg[pa.rank] + slot_off + px * 4);
+    const int W = pa.world;
+    const int64_t slot_off = (int64_t)(seq & 1u) * peer_slot_bytes(P, W);
+    const int64_t flags_off = slot_off + (int64_t)W * px * 4;    // flags[world][PEER_NB] behind data[world][px]
+    if (threadIdx.x == 0) s_fail = 0u;
     pdl_trigger();
     pdl_wait();
     double acc = 0.0;
@@ -358,12 +367,15 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel
     }
     part[pt][col] = acc;
     __syncthreads();
-    // ---- publish this rank's column block (and, from block 0, its 8 diagnostics)
+    // ---- push this rank's column block (and, from block 0, its 8 diagnostics) into EVERY rank's buffer, row [rank]
     if (pt == 0 && i < P) {
         double t = part[0][col];
 #pragma unroll
         for (int q = 1; q < RED_PARTS; q++) t += part[q][col];
-        my_data[i] = (float)t;
+        const float g = (float)t;
+#pragma unroll
+        for (int r = 0; r < PEER_MAX; r++)
+            if (r < W) st_sys_f32(reinterpret_cast<float*>(pa.xchg[r] + slot_off) + (int64_t)pa.rank * px + i, g);
     }
     if (blockIdx.x == 0 && threadIdx.x >= 64 && threadIdx.x < 96) {
         const int l = threadIdx.x - 64;
@@ -382,39 +394,47 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel
 #pragma unroll
             for (int q = 0; q < 8; q++)
                 if (q == l) dv = d8[q];
-            my_data[px - 64 + l] = dv;
+#pragma unroll
+            for (int r = 0; r < PEER_MAX; r++)
+                if (r < W) st_sys_f32(reinterpret_cast<float*>(pa.xchg[r] + slot_off) + (int64_t)pa.rank * px + px - 64 + l, dv);
         }
     }
-    // release: the CTA barrier orders every thread's data stores before thread 0's system-scope fence (fences are
-    // cumulative), so ONE fence per CTA publishes the block - a fence per thread cost ~10 us per launch
+    // release: the CTA barrier orders every thread's data stores before the flag writers' system-scope fences (fences
+    // are cumulative); thread r then raises flags[rank][block] in rank r's buffer
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < W) {
         __threadfence_system();
-        st_sys_u32(my_flags + blockIdx.x, seq);
+        st_sys_u32(reinterpret_cast<unsigned*>(pa.xchg[threadIdx.x] + flags_off) + pa.rank * PEER_NB + blockIdx.x, seq);
     }
-    // ---- wait for the same block of every peer (bounded spin: a missing peer sets *err instead of hanging the GPU)
-    if (threadIdx.x < pa.world && threadIdx.x != pa.rank) {
-        const unsigned* pf = reinterpret_cast<const unsigned*>(pa.xchg[threadIdx.x] + slot_off + px * 4) + blockIdx.x;
+    // ---- wait, in LOCAL memory, for the same block of every rank (bounded spin: a missing peer sets *err, no GPU hang)
+    if (threadIdx.x < W) {
+        const unsigned* pf = reinterpret_cast<const unsigned*>(pa.xchg[pa.rank] + flags_off) + threadIdx.x * PEER_NB + blockIdx.x;
         const long long t0 = clock64();
+        const long long lim = pa.spin_cycles > 0 ? pa.spin_cycles : 40000000000ll;
         while ((int)(ld_sys_u32(pf) - seq) < 0) {
-            if (clock64() - t0 > 4000000000ll) { atomicExch(pa.err, 1u); break; }
+            if (clock64() - t0 > lim) { atomicExch(pa.err, 1u); s_fail = 1u; break; }
         }
         __threadfence_system();   // acquire side: only the polling threads, then the barrier hands it to the CTA
     }
     __syncthreads();
     // ---- totals in rank order
+    const float* mine = reinterpret_cast<const float*>(pa.xchg[pa.rank] + slot_off);
     double sq = 0.0;
     if (pt == 0 && i < P) {
+        float v[PEER_MAX];
+#pragma unroll
+        for (int r = 0; r < PEER_MAX; r++) v[r] = r < W ? ld_sys_f32(mine + (int64_t)r * px + i) : 0.0f;   // loads in flight together
         float g = 0.0f;
-        for (int r = 0; r < pa.world; r++) g += ld_sys_f32(reinterpret_cast<const float*>(pa.xchg[r] + slot_off) + i);
+#pragma unroll
+        for (int r = 0; r < PEER_MAX; r++)
+            if (r < W) g += v[r];
         grads_out[i] = g;
         sq = (double)g * (double)g;
     }
     if (blockIdx.x == 0 && threadIdx.x >= 64 && threadIdx.x < 72) {
         const int l = threadIdx.x - 64;
         float dv = 0.0f;
-        for (int r = 0; r < pa.world; r++)
-            dv += ld_sys_f32(reinterpret_cast<const float*>(pa.xchg[r] + slot_off) + px - 64 + l);
+        for (int r = 0; r < W; r++) dv += ld_sys_f32(mine + (int64_t)r * px + px - 64 + l);
         if (diag_out) diag_out[l] = dv;
         if (f.diag_hist) f.diag_hist[l] = dv;
     }
@@ -431,13 +451,16 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel
         __threadfence();
         atomicAdd(ticket, 1u);
         const long long t1 = clock64();
+        const long long lim = pa.spin_cycles > 0 ? pa.spin_cycles : 40000000000ll;
         while (*reinterpret_cast<volatile unsigned*>(ticket) < gridDim.x) {
-            if (clock64() - t1 > 4000000000ll) { atomicExch(pa.err, 1u); break; }
+            if (clock64() - t1 > lim) { atomicExch(pa.err, 1u); s_fail = 1u; break; }
             __nanosleep(32);
         }
         __threadfence();
     }
     __syncthreads();
+    // a rank that missed a peer (this CTA or any other: *err is device-wide and sticky) must not step on a partial sum
+    const bool failed = s_fail != 0u || *reinterpret_cast<volatile unsigned*>(pa.err) != 0u;
     double ss = 0.0;
     for (int b = threadIdx.x; b < (int)gridDim.x; b += RED_COLS * RED_PARTS) ss += __ldcg(sq_part + b);
 #pragma unroll
@@ -459,7 +482,7 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel
     const float omb1 = (float)(1.0 - b1), omb2 = (float)(1.0 - b2);
     const float sq_bc2 = (float)sqrt(bc2);
     const float neg_step = (float)(-((double)lr / bc1));
-    if (pt == 0 && i < P) {
+    if (pt == 0 && i < P && !failed) {
         float gg = grads_out[i];
         if (cf != 1.0f) gg = __fmul_rn(gg, cf);
         const float p = __fmul_rn(f.params[i], decay);
@@ -478,14 +501,14 @@ static inline void launch_reduce(const UpdArgs& a, int grid, int P, float* grads
     const int blocks = (P + RED_COLS - 1) / RED_COLS;
     if (fuse && peer) {
         char* tail = reinterpret_cast<char*>(a.dpart) + (size_t)UPD_MAX_GRID * UPD_NDIAG * sizeof(double);
-        launch_pdl(false, reduce_peer_apply_kernel, dim3(blocks), dim3(RED_COLS * RED_PARTS), 0, st, (const float*)a.slabs,
+        launch_pdl((g_pdl & 2) != 0, reduce_peer_apply_kernel, dim3(blocks), dim3(RED_COLS * RED_PARTS), 0, st, (const float*)a.slabs,
                    (const double*)a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out,
                    *fuse, *peer, reinterpret_cast<unsigned*>(tail), reinterpret_cast<double*>(tail + 64));
         return;
     }
     if (fuse) {
         char* tail = reinterpret_cast<char*>(a.dpart) + (size_t)UPD_MAX_GRID * UPD_NDIAG * sizeof(double);
-        launch_pdl(true, reduce_apply_kernel, dim3(blocks), dim3(RED_COLS * RED_PARTS), 0, st, (const float*)a.slabs,
+        launch_pdl((g_pdl & 1) != 0, reduce_apply_kernel, dim3(blocks), dim3(RED_COLS * RED_PARTS), 0, st, (const float*)a.slabs,
                    (const double*)a.dpart, grid, P, slab_stride(P), a.inv_n, a.hp.ent_coef, a.hp.vf_coef, grads_out, diag_out,
                    *fuse, reinterpret_cast<unsigned*>(tail), reinterpret_cast<double*>(tail + 64),
                    blocks <= (sm_count() > 0 ? sm_count() : 0));
@@ -559,7 +582,9 @@ int ppo::update_minibatch_fused(const float* params, const ppo_dims* dims, const
     UpdArgs a{};
     if (pf) a.pf = *pf;
     a.rec = reinterpret_cast<const float4*>(rec);
-    a.pdl = peer ? 0 : 1;   // measured on 2 GPUs: early launches next to the peer-polling kernel cost 7 % (4.03 vs 3.77 ms)
+    // programmatic dependent launch of the chain: bit 0 of ppo_debug_pdl on one GPU, bit 1 next to the peer exchange (with
+    // the PULL exchange early launches cost 7 % on 2 GPUs, 4.03 vs 3.77 ms; the push exchange polls local memory only)
+    a.pdl = peer ? ((g_pdl & 2) != 0) : ((g_pdl & 1) != 0);
     if (peer) {
         Dims dd;
         if (int rc = make_dims(dims, &dd)) return rc;
@@ -593,6 +618,13 @@ int ppo::update_minibatch_fused(const float* params, const ppo_dims* dims, const
             return PPO_OK;
         }
         if (rc != PPO_ERR_UNSUPPORTED) return rc;
+        const int rc2 = launch_update_h256(a, mode == PPO_MATH_BF16 ? 1 : 0, &grid, st);
+        if (rc2 == PPO_OK) {
+            launch_reduce(a, grid, P, grads_out, diag_out, st, fuse, peer);
+            PPO_LAUNCH_CHECK();
+            return PPO_OK;
+        }
+        if (rc2 != PPO_ERR_UNSUPPORTED) return rc2;
     }
     switch (a.d.H) {
         case 64: return launch_update<64, 64>(a, grads_out, diag_out, st, fuse, peer);

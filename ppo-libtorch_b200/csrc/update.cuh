@@ -24,6 +24,8 @@ struct FuseAdam {
     float max_grad_norm;
     float* norm_out;
     float* diag_hist;   // 8 floats of this optimiser step
+    unsigned* err;      // optional device flag set (and the step skipped) when the intra-GPU ticket spin times out
+    long long spin_cycles;   // 0 = default
 };
 // Slab reduction + clip + AdamW executed by the update kernel itself behind a grid-wide barrier (update_tc.cu:
 // fused_reduce_apply) instead of a second launch.  on != 0 only when every CTA of the launch is resident and there are at
@@ -65,19 +67,25 @@ struct UpdArgs {
 };
 
 // Data-parallel variant of the fused tail: the allreduce happens INSIDE the reduction kernel over peer memory (NVLink
-// P2P loads of the other ranks' exchange buffers, mapped with CUDA IPC), so gradient exchange + clip + AdamW is one launch
-// per rank instead of reduce_kernel -> ncclAllReduce -> clip_adamw_kernel.  Exchange buffer of a rank (one cudaMalloc):
-// two slots (optimiser step parity), each {data[PEER_PX(P)] floats, flags[PEER_NB] uint32}: CTA b publishes its 64 reduced
-// columns into data and then stores the step number into flags[b] (system-scope release); it waits until flags[b] of
-// every peer reached the step, sums the W column blocks in rank order (=> bit-identical totals on every rank) and goes on
-// as the single-GPU kernel.  Slot reuse two steps later is safe: a peer publishes step s+1 only after its step-s reads.
+// P2P stores into the other ranks' exchange buffers, mapped with CUDA IPC), so gradient exchange + clip + AdamW is one
+// launch per rank instead of reduce_kernel -> ncclAllReduce -> clip_adamw_kernel.  PUSH model: exchange buffer of a rank
+// (one cudaMalloc) = two slots (optimiser step parity), each {data[world][peer_px(P)] floats, flags[world][PEER_NB] uint32}.
+// CTA b of rank r STORES its 64 reduced columns into data[r] of EVERY rank's buffer (its own included), fences at system
+// scope and stores the step number into flags[r][b] of every rank; it then polls only its OWN buffer's flags[*][b] (local
+// memory) and sums the world's column blocks in rank order (=> bit-identical totals on every rank).  One one-way NVLink
+// latency per optimiser step; the pull model this replaces paid two dependent round trips (remote flag poll, then remote
+// column loads).  Slot reuse two steps later is safe: a peer publishes step s+1 only after its step-s reads.
 constexpr int PEER_MAX = 8, PEER_NB = 256;
 __host__ __device__ inline int64_t peer_px(int P) { return (((int64_t)P + 63) & ~(int64_t)63) + 64; }   // + diagnostics
-__host__ __device__ inline int64_t peer_slot_bytes(int P) { return peer_px(P) * 4 + PEER_NB * 4; }
+__host__ __device__ inline int64_t peer_slot_bytes(int P, int world) {
+    return (int64_t)world * (peer_px(P) * 4 + PEER_NB * 4);
+}
 struct PeerArgs {
     int world, rank;
     char* xchg[PEER_MAX];   // every rank's exchange buffer as mapped in THIS process (xchg[rank] = the local one)
-    unsigned* err;          // device flag set when a peer did not arrive within the spin limit
+    unsigned* err;          // local device flag: set when a peer did not arrive within the spin limit (sticky: once set,
+                            // every later optimiser step is skipped so that ranks cannot step on partial gradients)
+    long long spin_cycles;  // spin limit in SM cycles (ppo_set_spin_timeout_ms)
 };
 constexpr int RED_COLS = 64, RED_PARTS = 4;
 __host__ __device__ inline int64_t upd_tail_bytes(int P) { return 64 + (int64_t)((P + RED_COLS - 1) / RED_COLS) * 8; }
@@ -97,5 +105,9 @@ int launch_update_tc(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st, const 
 
 bool update_tc_supported(const Dims& d);     // update_tc.cu: hidden = 64 envelope
 bool update_h256_supported(const Dims& d);   // update_h256.cu: hidden = 256 envelope
+// update_h256.cu: forward / loss / backward kernel + dW2 GEMM kernel for hidden = 256; PPO_ERR_UNSUPPORTED outside the envelope
+int launch_update_h256(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st);
+// grows the 16-bit activation scratch of the hidden = 256 path to `mb_rows` minibatch rows (call outside stream capture)
+int h256_reserve(int64_t mb_rows);
 
 }  // namespace ppo

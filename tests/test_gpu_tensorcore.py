@@ -238,6 +238,93 @@ def test_update_tc_config_e_shard_rows(P, orc, math_mode):
     np.testing.assert_allclose(diag.cpu().numpy()[:5], od[:5], rtol=LTOL[2], atol=LTOL[2] * 1e-2)
 
 
+# ------------------------------------------------------------------------------- hidden = 256 rollout on the tensor core
+# Stated tolerance of the 16-bit rollout (rollout_h256.cu) against the fp32 oracle: layer 1 is fp32, h1 / W2 are rounded to
+# fp16 (11 significant bits, the mantissa of the reference's own TF32 CUDA mode), tanh is the 2^-11 MUFU approximation:
+# values and log-probs within 5e-3 (absolute + relative), sampled actions identical unless the uniform lies within 4e-3
+# of a CDF edge.  Everything downstream of the sampled action (env transition, truncation, auto-reset, episode log,
+# GAE on the stored rows) is exact.
+ROLL_TOL = 5e-3
+ROLL_BAND = 4e-3
+
+
+@pytest.mark.parametrize("kind,O,nvec,masked,n,T", [(1, 2, [3], False, 300, 6), (0, 4, [2], False, 1100, 5),
+                                                    (1, 2, [3], True, 129, 7)])
+def test_rollout_h256_tensorcore_vs_oracle(P, orc, request, math_mode, kind, O, nvec, masked, n, T):
+    import sys, os
+    sys.path.insert(0, os.path.dirname(__file__))
+    from philox_np import reset_uniforms, sample_uniforms
+    H, seed, counter, base, max_ep = 256, 99, 500, 32, 5
+    K, heads = sum(nvec), len(nvec)
+    math_mode(2)
+    P.capi.load().ppo_debug_rollout_impl(3)                        # force the tensor-core tiles at any env count
+    request.addfinalizer(lambda: P.capi.load().ppo_debug_rollout_impl(1))
+    params = P.orthogonal_init_params(O, H, nvec, seed=11)
+    params[-K:] = np.linspace(-0.3, 0.3, K)
+    u0 = np.random.default_rng(1).uniform(size=(n, 4)).astype(np.float32)
+    state, ep_len, ep_ret, _ = P.ops.env_reset(kind, n, uniforms=dev(u0))
+    next_done = torch.zeros(n, device="cuda")
+    st0 = state.cpu().numpy().T.copy()
+    out = P.ops.rollout(dev(params), O, H, nvec, kind, state, ep_len, ep_ret, next_done, T, max_ep, 0.98, 0.95,
+                        masked=masked, seed=seed, counter=counter, env_id_base=base)
+    o = {k: (v.cpu().numpy() if v is not None else None) for k, v in out.items()}
+    assert np.array_equal(o["obs"][0], st0)
+    o_len = np.zeros(n, np.int32)
+    o_ret = np.zeros(n, np.float32)
+    prev_done = np.zeros(n, np.float32)
+    ids = np.arange(n) + base
+    n_fin = 0
+    for t in range(T):
+        obs_t = o["obs"][t]
+        assert np.array_equal(o["dones"][t], prev_done)
+        logits, val = orc.mlp_forward(params, O, H, K, obs_t)
+        np.testing.assert_allclose(o["values"][t], val, rtol=ROLL_TOL, atol=ROLL_TOL)
+        u = sample_uniforms(seed, ids, counter + t, heads)
+        mask = np.ones((n, K), np.uint8) if masked else None
+        oa, _, _, pr, _ = orc.categorical(logits, nvec, mask=mask, uniforms=u, want_probs=True)
+        edge = np.min(np.abs(np.cumsum(pr[:, :nvec[0]].astype(np.float64), 1) - u[:, :1]), 1) < ROLL_BAND
+        ga = o["actions"][t]
+        assert np.all((ga == oa).all(1) | edge)
+        assert edge.mean() < 0.05
+        _, olp2, _ = orc.categorical(logits, nvec, mask=mask, actions=ga)
+        np.testing.assert_allclose(o["logprobs"][t], olp2, rtol=ROLL_TOL, atol=ROLL_TOL)
+        if masked:
+            assert np.all(o["masks"][t] == 1)
+        ru = reset_uniforms(seed, ids, counter + t)
+        st = obs_t.copy()
+        oobs, orew, odone, ofl, ofr = orc.env_step(kind, st, o_len, o_ret, ga[:, 0].astype(np.int32), max_ep, ru)
+        assert np.array_equal(o["rewards"][t], orew)
+        assert np.array_equal(o["fin_len"][t], np.asarray(ofl).astype(np.int32))
+        nxt = o["obs"][t + 1] if t + 1 < T else state.cpu().numpy().T
+        np.testing.assert_allclose(nxt, oobs, rtol=1e-6, atol=1e-7)
+        prev_done = odone
+        n_fin += int((ofl > 0).sum())
+    assert np.array_equal(next_done.cpu().numpy(), prev_done)
+    assert np.array_equal(ep_len.cpu().numpy(), o_len)
+    assert n_fin > 0 and o["ep_stats"][0] == n_fin
+    _, nval = orc.mlp_forward(params, O, H, K, state.cpu().numpy().T.copy())
+    np.testing.assert_allclose(o["next_value"], nval, rtol=ROLL_TOL, atol=ROLL_TOL)
+    oadv, oret = orc.gae(o["rewards"], o["values"], o["dones"], o["next_value"], prev_done, 0.98, 0.95)
+    assert np.array_equal(o["adv"], oadv) and np.array_equal(o["ret"], oret)
+
+
+def test_trainer_h256_mountaincar_default_mode(P):
+    """BASELINE configs[2]'s shape class (MountainCar, 2 x 256 MLP) through the trainer in the default 16-bit mode:
+    tensor-core rollout + value pass + hidden = 256 update pipeline, CUDA graph replay, finite and deterministic."""
+    kw = dict(env_kind=P.capi.ENV_MOUNTAINCAR, obs_dim=2, hidden=256, nvec=(3,), num_envs=2048, num_steps=16,
+              num_minibatches=4, update_epochs=2, max_episode_steps=200, seed=3)
+    assert P.ops.update_path(2, 256, [3]) == 2
+    outs = []
+    for graph in (False, True):
+        tr = P.Trainer(use_cuda_graph=graph, **kw)
+        rs = [tr.iterate(1e-3) for _ in range(3)]
+        outs.append((tr.get_params(), rs))
+        tr.close()
+    for p, rs in outs:
+        assert np.isfinite(p).all() and all(np.isfinite(r["loss"]) and r["grad_norm"] > 0 for r in rs)
+    assert np.array_equal(outs[0][0], outs[1][0]), "graph replay and eager launches must give identical parameters"
+
+
 # ------------------------------------------------------------------------------- the trainer in its default mode
 def _run_trainer(P, mode, iters, **kw):
     prev = P.ops.get_math_mode()
