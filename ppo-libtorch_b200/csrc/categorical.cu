@@ -106,9 +106,171 @@ __global__ void __launch_bounds__(CAT_ROWS) categorical_kernel(const CatArgs a) 
     }
 }
 
+// ---- warp-cooperative kernel: one (row, head) per lane --------------------------------------------------------------------
+// The row-per-thread kernel above spends ~4 300 thread-instructions per 21-logit row (IEEE expf / logf / division per
+// logit, twice) and runs at 16 % of the HBM roofline.  Here a lane owns ONE head of one row (heads padded to HP = 1, 2, 4 or
+// 8 lanes, 32 / HP rows per pass, 32 rows per warp), its <= 8 logits stay in registers, the row's log-prob and entropy are
+// xor-shuffle sums over the row's lanes, and no shared-memory staging is needed: the lanes of a pass read one contiguous
+// span of logits.  Arithmetic: ex2 / lg2 / rcp approximations (2 ulp: probabilities within 1e-6, log-probs within 1e-6 of
+// the IEEE path - inside the 4e-6 / 1e-5 parity bounds).  The ONE place where a last-bit difference is visible is the
+// inverse-CDF compare u < cumsum(p): a draw closer than CAT_BAND to a CDF edge is re-evaluated with the IEEE routines
+// (categorical.cuh: the oracle's operation order), so sampled actions are those of the row-per-thread kernel.
+// Philox: lane l draws the blocks of row (base + l) once per 32 rows; a pass fetches its uniform with shuffles.
+constexpr float CAT_BAND = 4e-6f;
+constexpr int CAT_MAXKH = 8;
+
+template <int HP>
+__global__ void __launch_bounds__(256) categorical_lane_kernel(const CatArgs a) {
+    constexpr int RPW = 32 / HP;
+    const int lane = threadIdx.x & 31;
+    const int64_t row_base = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32;
+    if (row_base >= a.n) return;
+    const int h = lane % HP, rl = lane / HP;
+    const int heads = a.heads, K = a.K;
+    const bool hon = h < heads;
+    int off = 0;
+#pragma unroll
+    for (int hh = 0; hh < PPO_MAX_HEADS; hh++)
+        if (hh < h && hh < heads) off += a.nvec[hh];
+    const int Kh = hon ? a.nvec[h] : 0;
+    const bool masked = a.mask != nullptr;
+    const bool sample = a.actions_in == nullptr;
+    const bool philox = sample && a.uniforms == nullptr;
+    const bool ref_quirk = !masked && a.entropy_mode == PPO_ENTROPY_REFERENCE;
+
+    uint32_t w[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // this lane's ROW (row_base + lane): uniforms of heads 0..7
+    if (philox && row_base + lane < a.n) {
+        uint32_t r[4];
+        Philox::gen(a.seed, (uint32_t)(row_base + lane), RNG_STREAM_SAMPLE, (uint32_t)a.counter, (uint32_t)(a.counter >> 32), r);
+        w[0] = r[0]; w[1] = r[1]; w[2] = r[2]; w[3] = r[3];
+        if (heads > 4) {
+            Philox::gen(a.seed, (uint32_t)(row_base + lane), RNG_STREAM_SAMPLE | (1u << 8), (uint32_t)a.counter,
+                        (uint32_t)(a.counter >> 32), r);
+            w[4] = r[0]; w[5] = r[1]; w[6] = r[2]; w[7] = r[3];
+        }
+    }
+#pragma unroll 1
+    for (int p = 0; p < HP; p++) {
+        const int r_local = p * RPW + rl;
+        const int64_t row = row_base + r_local;
+        const bool on = hon && row < a.n;
+        float u = 0.0f;
+        if (philox) {
+            uint32_t uw = 0u;
+#pragma unroll
+            for (int hh = 0; hh < PPO_MAX_HEADS; hh++) {
+                const uint32_t t = __shfl_sync(0xffffffffu, w[hh], r_local);
+                if (hh == h) uw = t;
+            }
+            u = Philox::u01(uw);
+        } else if (sample && on) {
+            u = __ldg(a.uniforms + row * heads + h);
+        }
+        int pick = (!sample && on) ? __ldg(a.actions_in + row * heads + h) : -1;
+        float xm[CAT_MAXKH], e[CAT_MAXKH];
+        uint32_t vbits = 0u;
+        const float* xp = a.logits + row * K + off;
+        const uint8_t* mp = a.mask + row * K + off;
+        float mx = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < CAT_MAXKH; j++) {
+            xm[j] = -INFINITY;
+            if (on && j < Kh) {
+                const bool v = !masked || __ldg(mp + j) != 0;
+                xm[j] = v ? __ldg(xp + j) : -1e8f;      // CategoricalMasked.cpp:35
+                vbits |= (uint32_t)v << j;
+                mx = fmaxf(mx, xm[j]);
+            }
+        }
+        float sum = 0.0f;
+#pragma unroll
+        for (int j = 0; j < CAT_MAXKH; j++) {
+            e[j] = 0.0f;
+            if (j < Kh) {
+                asm("ex2.approx.f32 %0, %1;" : "=f"(e[j]) : "f"((xm[j] - mx) * 1.4426950408889634f));
+                sum += e[j];
+            }
+        }
+        float rs, lg;
+        asm("rcp.approx.f32 %0, %1;" : "=f"(rs) : "f"(sum));
+        asm("lg2.approx.f32 %0, %1;" : "=f"(lg) : "f"(sum));
+        const float lse = fmaf(lg, 0.6931471805599453f, mx);
+        float c = 0.0f, acc = 0.0f;
+        int last_valid = 0, apick = -1;
+        bool near = false;
+#pragma unroll
+        for (int j = 0; j < CAT_MAXKH; j++) {
+            if (j < Kh) {
+                const float pj = e[j] * rs, lp = xm[j] - lse;
+                float t;
+                if (ref_quirk) {
+                    t = __fmul_rn(fmaxf(lp, FLT_MIN), pj);     // Categorical.cpp:114-117
+                } else {
+                    t = lp * pj;
+                    if (!((vbits >> j) & 1u) || pj == 0.0f) t = 0.0f;
+                }
+                acc += t;
+                if (pj > 0.0f) last_valid = j;
+                c += pj;
+                near = near || fabsf(u - c) < CAT_BAND;
+                if (apick < 0 && u < c) apick = j;
+                if (a.probs_out && on) a.probs_out[row * K + off + j] = pj;
+            }
+        }
+        if (sample) {
+            pick = apick < 0 ? last_valid : apick;
+            if (near && on) {   // within the band of a CDF edge: the oracle's IEEE operation order decides
+                float mxe = -INFINITY;
+#pragma unroll
+                for (int j = 0; j < CAT_MAXKH; j++)
+                    if (j < Kh) mxe = fmaxf(mxe, xm[j]);
+                float se = 0.0f;
+#pragma unroll
+                for (int j = 0; j < CAT_MAXKH; j++)
+                    if (j < Kh) se = __fadd_rn(se, expf(__fsub_rn(xm[j], mxe)));
+                float ce = 0.0f;
+                int ae = -1, lv = 0;
+#pragma unroll
+                for (int j = 0; j < CAT_MAXKH; j++) {
+                    if (j < Kh) {
+                        const float pe = __fdiv_rn(expf(__fsub_rn(xm[j], mxe)), se);
+                        if (pe > 0.0f) lv = j;
+                        ce = __fadd_rn(ce, pe);
+                        if (ae < 0 && u < ce) ae = j;
+                    }
+                }
+                pick = ae < 0 ? lv : ae;
+            }
+        }
+        float lpa = 0.0f;
+#pragma unroll
+        for (int j = 0; j < CAT_MAXKH; j++)
+            if (j == pick) lpa = xm[j] - lse;
+        float lpr = on ? lpa : 0.0f, enr = on ? -acc : 0.0f;
+#pragma unroll
+        for (int o = 1; o < HP; o <<= 1) {
+            lpr += __shfl_xor_sync(0xffffffffu, lpr, o);
+            enr += __shfl_xor_sync(0xffffffffu, enr, o);
+        }
+        if (on && a.actions_out) a.actions_out[row * heads + h] = pick;
+        if (h == 0 && row < a.n) {
+            if (a.logprob) a.logprob[row] = lpr;
+            if (a.entropy) a.entropy[row] = enr;
+        }
+    }
+}
+
+static int g_cat_impl = 1;   // ppo_debug_categorical_impl: 0 = row-per-thread kernel for every shape
+
 }  // namespace ppo
 
 using namespace ppo;
+
+extern "C" int ppo_debug_categorical_impl(int impl) {
+    g_cat_impl = impl;
+    return PPO_OK;
+}
+
 
 extern "C" int ppo_categorical(int n, int heads, const int32_t* h_nvec, const float* logits, const uint8_t* mask,
                                const int32_t* actions_in, const float* uniforms, uint64_t seed, uint64_t counter,
@@ -129,6 +291,19 @@ extern "C" int ppo_categorical(int n, int heads, const int32_t* h_nvec, const fl
     a.logits = logits; a.mask = mask; a.actions_in = actions_in; a.uniforms = uniforms;
     a.seed = seed; a.counter = counter; a.entropy_mode = entropy_mode;
     a.actions_out = actions_out; a.logprob = logprob_out; a.entropy = entropy_out; a.probs_out = probs_out;
+    int maxk = 0;
+    for (int h = 0; h < heads; h++) maxk = a.nvec[h] > maxk ? a.nvec[h] : maxk;
+    if (g_cat_impl && maxk <= CAT_MAXKH) {   // a (row, head) per lane; heads padded to a power of two
+        const int blocks = (n + 255) / 256;
+        const int hp = heads <= 1 ? 1 : (heads <= 2 ? 2 : (heads <= 4 ? 4 : 8));
+        cudaStream_t st = as_stream(stream);
+        if (hp == 1) categorical_lane_kernel<1><<<blocks, 256, 0, st>>>(a);
+        else if (hp == 2) categorical_lane_kernel<2><<<blocks, 256, 0, st>>>(a);
+        else if (hp == 4) categorical_lane_kernel<4><<<blocks, 256, 0, st>>>(a);
+        else categorical_lane_kernel<8><<<blocks, 256, 0, st>>>(a);
+        PPO_LAUNCH_CHECK();
+        return PPO_OK;
+    }
     const int ld = a.K | 1;
     const size_t smem = (size_t)CAT_ROWS * ld * 4 + (size_t)CAT_ROWS * heads * 8 + (size_t)CAT_ROWS * a.K + 16;
     const int blocks = (n + CAT_ROWS - 1) / CAT_ROWS;
