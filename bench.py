@@ -385,7 +385,7 @@ def time_trainer(torch, dist, tr, K, W, flush, it0_total):
 
 
 UPDATE_PATHS = {0: "fp32 FMA kernels (update_kernel)", 1: "tcgen05, hidden = 64, one fused kernel (update_tc_kernel)",
-                2: "tcgen05, hidden = 256, per-layer pipeline (h256_fwd / h256_dx / h256_dw kernels)"}
+                2: "tcgen05, hidden = 256: update_h256_kernel (forward + loss + dX, one net per CTA) + dw2_h256_kernel (TMA-fed dW2 GEMM)"}
 
 
 def run_b200(args, wl_name):
@@ -453,7 +453,7 @@ def run_b200(args, wl_name):
     # one GPU / peer-memory DP: scalars, rollout, gae, all-epoch advantage statistics, row packing, per minibatch {update,
     # reduce+clip+AdamW}, explained variance.  NCCL DP: per epoch {permutation, moments, finalize}, per minibatch
     # {update, reduce, clip_adamw} (NCCL's own kernels are not counted: not ours).
-    upd_launches = {0: 1, 1: 1, 2: 6}.get(path, 1)      # kernels per minibatch gradient
+    upd_launches = {0: 1, 1: 1, 2: 2}.get(path, 1)      # kernels per minibatch gradient
     if world == 1 or exchange.startswith("peer"):
         packed = 1 if (len(wl["nvec"]) == 1 and wl["O"] <= 4 and wl["H"] in (64, 256)) else 0   # + ppo_pack_rows
         launches = 4 + packed + 1 + wl["E"] * wl["MB"] * (upd_launches + 1) + 1 + (1 if world > 1 else 0)   # + episode tail

@@ -120,6 +120,12 @@ int ppo_categorical(int n, int heads, const int32_t* h_nvec, const float* logits
                     float* logprob_out, float* entropy_out, float* probs_out,
                     ppo_stream_t stream);
 
+/* The distribution classes' public members (Distributions/Categorical.cpp:33-35, CategoricalMasked.cpp:35-40):
+ * logits_norm_out [n,sumK] = x' - logsumexp(x') per head, probs_out [n,sumK] = softmax(x') per head, x' = where(mask, x,
+ * -1e8).  Either output may be NULL. */
+int ppo_categorical_normalize(int n, int heads, const int32_t* h_nvec, const float* logits, const uint8_t* mask,
+                              float* logits_norm_out, float* probs_out, ppo_stream_t stream);
+
 /* ---- K1: fused actor-critic forward ------------------------------------------------------ */
 /* Agent::getActionAndValueDiscrete / getActionAndValueMasked (PPO/Agent.cpp:117-128,137-170)
  * = actor MLP + critic MLP + K2 in one launch.  obs [n,O].  actions_in NULL => sample.
@@ -349,37 +355,8 @@ int ppo_trainer_set_comm(ppo_trainer* t, ppo_comm* comm);
 int ppo_trainer_peer_handle(ppo_trainer* t, char* h_handle64);
 int ppo_trainer_set_peers(ppo_trainer* t, const char* h_handles, int world_size);
 
-/* ---- diagnostics ----------------------------------------------------------------------------- */
-/* Known-answer probe of the tcgen05 (16-bit operands, fp32 TMEM accumulator) building blocks the fused kernels
- * use (csrc/umma.cuh).  One 128-thread CTA, one GEMM with operands rounded to fp16 (fmt 0) or bf16 (fmt 1):
- * mode 0: D[128,64] = A[128,64] B[64,64]^T; 1: D = A B[64,64]; 2: D[64,64] = A^T B[128,64]; 3: D[64,16] = A^T B[128,16].
- * D receives the raw tensor-memory image [128 lanes][64 columns] (M = 64 results sit in lanes
- * (m % 16) + 32 (m / 16)).  No reference counterpart. */
-int ppo_debug_umma_probe(int mode, int fmt, const float* A, const float* B, float* D, ppo_stream_t stream);
-/* Same GEMM issued `reps` times back to back by one thread; d_cycles[0] (device int64) = SM clocks from the first issue
- * to the completion of the last (how fast the tensor pipe retires each operand layout). */
-/* Rollout kernel choice for hidden = 64: 1 (default) = register-resident-weights kernel, 0 = the generic tiled kernel
- * (what every other hidden width uses).  For A/B tests and benchmarks; no reference counterpart. */
-int ppo_debug_rollout_impl(int impl);
-/* 1 (default): trainers whose shape allows it (single head, unmasked, obs_dim <= 4) repack the rollout rows with
- * ppo_pack_rows once per iteration and the update kernel gathers records; 0: gather from the six row arrays. */
-int ppo_debug_pack_rows(int on);
-/* 1: on one GPU, when the update kernel's grid covers every 64-column block of the parameter vector, it runs the slab
- * reduction + clip_grad_norm_ + AdamW itself behind a grid-wide barrier (one launch per optimiser step); 0 (default): the
- * separate reduce_apply_kernel launch, which measured 1-2 % faster. */
-int ppo_debug_fuse_tail(int on);
-/* 1 (default): the update kernel and the reduction / optimiser kernel are launched with programmatic stream
- * serialization (each calls griddepcontrol.wait before reading its predecessor's output), so a launch overlaps the tail
- * of the kernel in front of it; 0: ordinary stream order. */
-int ppo_debug_pdl(int on);
-/* d_ts = device buffer of 8 int64 (NULL switches it off): CTA 0 / thread 0 of the hidden = 64 rollout kernel stamps the
- * SM clock at the six phase edges of rollout step 2 (tools/rollout_bench.py prints the deltas). */
-int ppo_debug_rollout_timeline(long long* d_ts);
-/* In-kernel timeline of the tensor-core update kernel: d_ts = device buffer of 256 int64 (NULL switches it off);
- * later launches stamp the SM clock of CTA 0, thread `who` at fixed points (tools/tc_timeline.py prints them). */
-int ppo_debug_tc_timeline(long long* d_ts, int who);
-int ppo_debug_umma_time(int mode, int fmt, const float* A, const float* B, float* D, int reps, long long* d_cycles,
-                        ppo_stream_t stream);
+/* Diagnostics, A/B switches and in-kernel timelines (ppo_debug_*) live in ppo_b200_debug.h: they are not part of the
+ * drop-in surface. */
 
 #ifdef __cplusplus
 }

@@ -77,6 +77,8 @@ _PROTOS = {
     "ppo_set_math_mode": (C.c_int, [C.c_int]),
     "ppo_get_math_mode": (C.c_int, []),
     "ppo_update_path": (C.c_int, [C.POINTER(Dims)]),
+    "ppo_categorical_normalize": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p]),
     "ppo_adv_stats_all_epochs": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint64,
                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ppo_trainer_peer_handle": (C.c_int, [C.c_void_p, C.c_char_p]),
@@ -84,6 +86,9 @@ _PROTOS = {
     "ppo_debug_rollout_impl": (C.c_int, [C.c_int]),
     "ppo_debug_pack_rows": (C.c_int, [C.c_int]),
     "ppo_debug_pdl": (C.c_int, [C.c_int]),
+    "ppo_debug_categorical_impl": (C.c_int, [C.c_int]),
+    "ppo_debug_adv_impl": (C.c_int, [C.c_int]),
+    "ppo_debug_h256_timeline": (C.c_int, [C.c_void_p]),
     "ppo_set_spin_timeout_ms": (C.c_int, [C.c_int64]),
     "ppo_debug_fuse_tail": (C.c_int, [C.c_int]),
     "ppo_trainer_last_episodes": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),

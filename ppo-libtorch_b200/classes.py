@@ -34,6 +34,7 @@ class Categorical:
         self._seed, self._calls = seed, 0
         self._emode = capi.ENTROPY_EXACT if exact_entropy else capi.ENTROPY_REFERENCE
         self._cache = None
+        self._norm = None
 
     def _eval(self, actions=None, uniforms=None):
         fresh = actions is None
@@ -55,9 +56,10 @@ class Categorical:
         return self._stats()[3]
 
     @property
-    def m_logits(self):           # logits - logsumexp (:33): log of the normalised probabilities, -inf-free where p > 0
-        p = self.m_probs
-        return torch.where(p > 0, torch.log(p), torch.full_like(p, -1e8 if self._masked else -float("inf")))
+    def m_logits(self):           # logits - logsumexp (:33), from the kernel (ppo_categorical_normalize): finite wherever the
+        if self._norm is None:    # reference's are (a masked logit reads -1e8 - lse, not log(0))
+            self._norm = ops.categorical_normalize(self._x, [self.m_num_events], mask=self._mask)[0]
+        return self._norm
 
     def sample(self, uniforms=None):
         """int64 [N]; `uniforms` [N] in [0,1) injects the draws (parity tests)"""

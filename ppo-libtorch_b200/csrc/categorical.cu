@@ -117,9 +117,11 @@ __global__ void __launch_bounds__(CAT_ROWS) categorical_kernel(const CatArgs a) 
 // (categorical.cuh: the oracle's operation order), so sampled actions are those of the row-per-thread kernel.
 // Philox: lane l draws the blocks of row (base + l) once per 32 rows; a pass fetches its uniform with shuffles.
 constexpr float CAT_BAND = 4e-6f;
-constexpr int CAT_MAXKH = 8;
+constexpr int CAT_MAXKH_LIMIT = 8;
 
-template <int HP>
+// HP = lanes per row (heads padded to a power of two), CAT_MAXKH = compile-time bound of the logits per head (the
+// per-logit loops are fully unrolled and predicated on the lane's own head size)
+template <int HP, int CAT_MAXKH>
 __global__ void __launch_bounds__(256) categorical_lane_kernel(const CatArgs a) {
     constexpr int RPW = 32 / HP;
     const int lane = threadIdx.x & 31;
@@ -260,6 +262,28 @@ __global__ void __launch_bounds__(256) categorical_lane_kernel(const CatArgs a) 
     }
 }
 
+// m_logits = x' - logsumexp(x') and m_probs = softmax(x') (Categorical.cpp:33-35, CategoricalMasked.cpp:35-40) for the
+// distribution classes' public members: one thread per (row, head), IEEE routines of categorical.cuh
+__global__ void categorical_normalize_kernel(const CatArgs a, float* __restrict__ logits_out, float* __restrict__ probs_out) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int heads = a.heads;
+    if (t >= (int64_t)a.n * heads) return;
+    const int64_t row = t / heads;
+    const int h = (int)(t - row * heads);
+    int off = 0;
+    for (int hh = 0; hh < h; hh++) off += a.nvec[hh];
+    const int Kh = a.nvec[h];
+    const float* x = a.logits + row * a.K + off;
+    const bool masked = a.mask != nullptr;
+    const uint64_t mb = masked ? pack_mask(a.mask + row * a.K + off, Kh) : ~0ull;
+    const HeadStats s = head_stats(x, Kh, mb, masked);
+    for (int j = 0; j < Kh; j++) {
+        const float xm = masked_logit(x[j], !masked || ((mb >> j) & 1ull));
+        if (logits_out) logits_out[row * a.K + off + j] = head_logp(xm, s);
+        if (probs_out) probs_out[row * a.K + off + j] = head_prob(xm, s);
+    }
+}
+
 static int g_cat_impl = 1;   // ppo_debug_categorical_impl: 0 = row-per-thread kernel for every shape
 
 }  // namespace ppo
@@ -293,14 +317,19 @@ extern "C" int ppo_categorical(int n, int heads, const int32_t* h_nvec, const fl
     a.actions_out = actions_out; a.logprob = logprob_out; a.entropy = entropy_out; a.probs_out = probs_out;
     int maxk = 0;
     for (int h = 0; h < heads; h++) maxk = a.nvec[h] > maxk ? a.nvec[h] : maxk;
-    if (g_cat_impl && maxk <= CAT_MAXKH) {   // a (row, head) per lane; heads padded to a power of two
+    if (g_cat_impl && maxk <= CAT_MAXKH_LIMIT) {   // a (row, head) per lane; heads padded to a power of two
         const int blocks = (n + 255) / 256;
         const int hp = heads <= 1 ? 1 : (heads <= 2 ? 2 : (heads <= 4 ? 4 : 8));
+        const int mk = maxk <= 2 ? 2 : (maxk <= 3 ? 3 : (maxk <= 4 ? 4 : 8));
         cudaStream_t st = as_stream(stream);
-        if (hp == 1) categorical_lane_kernel<1><<<blocks, 256, 0, st>>>(a);
-        else if (hp == 2) categorical_lane_kernel<2><<<blocks, 256, 0, st>>>(a);
-        else if (hp == 4) categorical_lane_kernel<4><<<blocks, 256, 0, st>>>(a);
-        else categorical_lane_kernel<8><<<blocks, 256, 0, st>>>(a);
+#define CAT_LAUNCH(HPV, MKV) categorical_lane_kernel<HPV, MKV><<<blocks, 256, 0, st>>>(a)
+#define CAT_BY_MK(HPV) (mk == 2 ? CAT_LAUNCH(HPV, 2) : mk == 3 ? CAT_LAUNCH(HPV, 3) : mk == 4 ? CAT_LAUNCH(HPV, 4) : CAT_LAUNCH(HPV, 8))
+        if (hp == 1) CAT_BY_MK(1);
+        else if (hp == 2) CAT_BY_MK(2);
+        else if (hp == 4) CAT_BY_MK(4);
+        else CAT_BY_MK(8);
+#undef CAT_BY_MK
+#undef CAT_LAUNCH
         PPO_LAUNCH_CHECK();
         return PPO_OK;
     }
@@ -308,6 +337,26 @@ extern "C" int ppo_categorical(int n, int heads, const int32_t* h_nvec, const fl
     const size_t smem = (size_t)CAT_ROWS * ld * 4 + (size_t)CAT_ROWS * heads * 8 + (size_t)CAT_ROWS * a.K + 16;
     const int blocks = (n + CAT_ROWS - 1) / CAT_ROWS;
     categorical_kernel<<<blocks, CAT_ROWS, smem, as_stream(stream)>>>(a);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
+extern "C" int ppo_categorical_normalize(int n, int heads, const int32_t* h_nvec, const float* logits, const uint8_t* mask,
+                                         float* logits_norm_out, float* probs_out, ppo_stream_t stream) {
+    PPO_REQUIRE(n >= 0 && logits && h_nvec && (logits_norm_out || probs_out), "ppo_categorical_normalize: null argument");
+    PPO_REQUIRE(heads >= 1 && heads <= PPO_MAX_HEADS, "ppo_categorical_normalize: heads=%d out of [1,%d]", heads, PPO_MAX_HEADS);
+    CatArgs a{};
+    a.n = n; a.heads = heads; a.K = 0;
+    for (int h = 0; h < heads; h++) {
+        PPO_REQUIRE(h_nvec[h] >= 1 && h_nvec[h] <= 64, "ppo_categorical_normalize: nvec[%d]=%d", h, h_nvec[h]);
+        a.nvec[h] = h_nvec[h];
+        a.K += h_nvec[h];
+    }
+    PPO_REQUIRE(a.K <= PPO_MAX_LOGITS, "ppo_categorical_normalize: sum(nvec)=%d exceeds %d", a.K, PPO_MAX_LOGITS);
+    if (n == 0) return PPO_OK;
+    a.logits = logits; a.mask = mask;
+    const int64_t total = (int64_t)n * heads;
+    categorical_normalize_kernel<<<(unsigned)((total + 255) / 256), 256, 0, as_stream(stream)>>>(a, logits_norm_out, probs_out);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
 }

@@ -8,6 +8,7 @@
 #include <string>
 
 #include "../../include/ppo_b200.h"
+#include "../../include/ppo_b200_debug.h"
 
 namespace ppo {
 
@@ -137,6 +138,29 @@ __device__ inline uint32_t feistel(uint32_t x, int bits, const uint32_t (&k)[4])
         const int t = lb; lb = rb; rb = t;
     }
     return (l << rb) | r;
+}
+// inverse of feistel(): the rounds backwards (the halves' widths are back to (bits / 2, rest) after four rounds)
+__device__ inline uint32_t feistel_inv(uint32_t y, int bits, const uint32_t (&k)[4]) {
+    int lb = bits >> 1, rb = bits - lb;
+    uint32_t l = y >> rb, r = y & ((1u << rb) - 1u);
+#pragma unroll
+    for (int i = 3; i >= 0; i--) {
+        // this round produced (l, r) = (r_prev, l_prev ^ f(r_prev)) from widths (lb_prev, rb_prev) = (rb, lb)
+        const int plb = rb, prb = lb;
+        const uint32_t pr = l;
+        uint32_t f = (pr ^ k[i]) * 0x9E3779B1u;
+        f ^= f >> 15; f *= 0x85EBCA77u; f ^= f >> 13;
+        const uint32_t pl = r ^ (f & ((1u << plb) - 1u));
+        l = pl; r = pr;
+        lb = plb; rb = prb;
+    }
+    return (l << rb) | r;
+}
+// position of row j in the permuted order: perm_index(perm_position(j)) == j (cycle walking inverts the same way)
+__device__ inline int64_t perm_position(int64_t j, int64_t batch, int half_bits, const uint32_t (&k)[4]) {
+    uint32_t x = (uint32_t)j;
+    do { x = feistel_inv(x, half_bits, k); } while ((int64_t)x >= batch);
+    return (int64_t)x;
 }
 __device__ inline int64_t perm_index(int64_t i, int64_t batch, int half_bits, const uint32_t (&k)[4]) {
     uint32_t x = (uint32_t)i;

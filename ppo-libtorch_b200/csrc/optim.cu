@@ -319,9 +319,112 @@ __global__ void __launch_bounds__(ADV_THREADS) adv_moments_all_kernel(const floa
     }
 }
 
+
+// The same statistics from ONE coalesced pass per epoch over the advantages: row j sits at position perm_position(j) of
+// epoch e's order (the inverse of the keyed bijection), i.e. in minibatch position / mb_size.  adv_moments_all_kernel's
+// permuted 4-byte gathers are fine while `adv` is L2-resident (< ~30 M rows) but at the 134 M rows of BASELINE configs[4]
+// on one GPU every gather is a 32-byte DRAM sector: 34.8 ms of a 373 ms iteration, against E coalesced reads of the array
+// here.  Grid (epoch, chunk): a CTA sums its chunk's rows into per-minibatch registers (double), ws[e][mb][chunk]; the
+// last CTA of an epoch adds the chunks in fixed order => run-to-run identical.
+constexpr int ADV_MBMAX = 8;
+__global__ void __launch_bounds__(ADV_THREADS) adv_moments_all_coalesced_kernel(
+    const float* __restrict__ adv, int64_t batch, int mb_size, int n_mb, int n_epochs, int half_bits, uint64_t seed,
+    uint64_t epoch0, const uint64_t* __restrict__ d_epoch, double* __restrict__ ws, float* __restrict__ stats_out,
+    double* __restrict__ partial_out) {
+    __shared__ double sh[ADV_THREADS / 32];
+    __shared__ bool last;
+    const int e = blockIdx.x, c = blockIdx.y;
+    uint32_t key[4];
+    perm_keys(seed, epoch0 + (uint64_t)e + (d_epoch ? *d_epoch : 0ull), key);
+    const int64_t per = (((batch + ADV_SLICES - 1) / ADV_SLICES) + 3) & ~(int64_t)3;
+    const int64_t i0 = c * per, i1 = i0 + per < batch ? i0 + per : batch;
+    // fp64 adds issue at ~2 per clock and SM on this part (the first version, 16 predicated double adds per row, ran at
+    // 7 clocks per row): rows go into fp32 per-minibatch registers, flushed into the double accumulators every 32 rows
+    double s[ADV_MBMAX], q[ADV_MBMAX];
+    float sf[ADV_MBMAX], qf[ADV_MBMAX];
+#pragma unroll
+    for (int m = 0; m < ADV_MBMAX; m++) { s[m] = 0.0; q[m] = 0.0; sf[m] = 0.0f; qf[m] = 0.0f; }
+    const float inv_mb = 1.0f / (float)mb_size;
+    auto add = [&](float x, int64_t j) {
+        const int64_t pos = perm_position(j, batch, half_bits, key);
+        int mb = (int)((float)pos * inv_mb);                 // pos / mb_size: float estimate, corrected by one either way
+        if ((int64_t)mb * mb_size > pos) mb--;
+        else if ((int64_t)(mb + 1) * mb_size <= pos) mb++;
+        const float xx = x * x;
+#pragma unroll
+        for (int m = 0; m < ADV_MBMAX; m++) {
+            sf[m] += m == mb ? x : 0.0f;
+            qf[m] += m == mb ? xx : 0.0f;
+        }
+    };
+    auto flush = [&]() {
+#pragma unroll
+        for (int m = 0; m < ADV_MBMAX; m++) {
+            s[m] += (double)sf[m]; q[m] += (double)qf[m];
+            sf[m] = 0.0f; qf[m] = 0.0f;
+        }
+    };
+    int64_t i = i0 + threadIdx.x * 4;
+    int since = 0;
+    for (; i + 3 < i1; i += 4 * ADV_THREADS) {   // i0 and per are multiples of 4: 16-byte aligned vector loads
+        const float4 v = __ldg(reinterpret_cast<const float4*>(adv + i));
+        add(v.x, i); add(v.y, i + 1); add(v.z, i + 2); add(v.w, i + 3);
+        if (++since == 8) { flush(); since = 0; }
+    }
+    for (int64_t t = i; t < i1 && t < i + 4; t++) add(__ldg(adv + t), t);   // the ragged tail of the last chunk
+    flush();
+    const int n_all = n_epochs * n_mb;
+    unsigned int* tickets = reinterpret_cast<unsigned int*>(ws + (size_t)n_all * ADV_SLICES * 2);
+#pragma unroll
+    for (int m = 0; m < ADV_MBMAX; m++) {
+        if (m < n_mb) {
+            const double S = block_sum<ADV_THREADS>(s[m], sh);
+            const double Q = block_sum<ADV_THREADS>(q[m], sh);
+            if (threadIdx.x == 0) {
+                ws[((size_t)(e * n_mb + m) * ADV_SLICES + c) * 2 + 0] = S;
+                ws[((size_t)(e * n_mb + m) * ADV_SLICES + c) * 2 + 1] = Q;
+            }
+        }
+    }
+    if (threadIdx.x == 0) {
+        __threadfence();
+        last = (atomicAdd(tickets + e, 1u) == ADV_SLICES - 1);
+    }
+    __syncthreads();
+    if (!last || threadIdx.x >= n_mb) return;
+    __threadfence();
+    const int m = threadIdx.x, emb = e * n_mb + m;
+    double S = 0.0, Q = 0.0;
+    for (int k = 0; k < ADV_SLICES; k++) {
+        S += ws[((size_t)emb * ADV_SLICES + k) * 2 + 0];
+        Q += ws[((size_t)emb * ADV_SLICES + k) * 2 + 1];
+    }
+    int64_t cnt = batch - (int64_t)m * mb_size;
+    if (cnt > mb_size) cnt = mb_size;
+    if (cnt < 0) cnt = 0;
+    const double n = (double)cnt;
+    if (partial_out) {
+        partial_out[emb * 3 + 0] = n; partial_out[emb * 3 + 1] = S; partial_out[emb * 3 + 2] = Q;
+    }
+    if (stats_out) {
+        const double mean = cnt > 0 ? S / n : 0.0;
+        double var = (Q - n * mean * mean) / (n - 1.0);
+        if (var < 0.0) var = 0.0;
+        stats_out[emb * 2 + 0] = (float)mean;
+        stats_out[emb * 2 + 1] = (float)sqrt(var);
+    }
+    if (threadIdx.x == 0) tickets[e] = 0;   // leave the workspace zeroed for the next launch
+}
+int g_adv_impl = 1;   // ppo_debug_adv_impl: 0 = permuted-gather kernel for every shape
+
 }  // namespace ppo
 
 using namespace ppo;
+
+extern "C" int ppo_debug_adv_impl(int impl) {
+    g_adv_impl = impl;
+    return PPO_OK;
+}
 
 namespace ppo {
 int clip_adamw_launch(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_params, float lr,
@@ -520,6 +623,15 @@ extern "C" int ppo_adv_stats_all_epochs(const float* adv, int64_t batch, int mb_
                 "ppo_adv_stats_all_epochs: bad arguments");
     PPO_REQUIRE(stats_out || partial_out, "ppo_adv_stats_all_epochs: no output requested");
     if (n_mb == 0 || n_epochs == 0) return PPO_OK;
+    // one coalesced pass per epoch once the advantages outgrow L2 (the permuted gathers turn into DRAM sectors); rows of
+    // a partial minibatch (batch % n_mb != 0) are handled alike: position / mb_size may reach n_mb - 1 only
+    if (g_adv_impl && n_mb <= ADV_MBMAX && n_epochs <= 1024 && batch >= (1 << 22)) {
+        double* ws = reinterpret_cast<double*>(workspace);
+        adv_moments_all_coalesced_kernel<<<dim3(n_epochs, ADV_SLICES), ADV_THREADS, 0, as_stream(stream)>>>(
+            adv, batch, mb_size, n_mb, n_epochs, perm_half_bits(batch), seed, epoch0, d_epoch, ws, stats_out, partial_out);
+        PPO_LAUNCH_CHECK();
+        return PPO_OK;
+    }
     adv_moments_all_kernel<<<dim3(n_mb * n_epochs, ADV_SLICES), ADV_THREADS, 0, as_stream(stream)>>>(
         adv, batch, mb_size, n_mb, n_epochs, perm_half_bits(batch), seed, epoch0, d_epoch,
         reinterpret_cast<double*>(workspace), stats_out, partial_out);

@@ -77,6 +77,14 @@ struct H256Args {
     int ntiles;
 };
 
+// optional in-kernel timeline (ppo_debug_h256_timeline): SM clock stamps of CTA 0, thread 0 at the phase edges of its
+// first 4 tiles, 16 slots per tile (tools/h256_timeline.py prints the deltas)
+__device__ long long* g_h256_ts = nullptr;
+#define H_TS(slot)                                                                        \
+    do {                                                                                  \
+        if (ts_buf && tile_no < 4) ts_buf[tile_no * 16 + (slot)] = clock64();             \
+    } while (0)
+
 // tensor-memory map of update_h256_kernel: Z (forward pre-activations, then dX) in columns 0..255; the skinny
 // accumulators, 16 columns each, at 256 + 16 * (moment * 2 + jb): moment 0 = X holds h2 (cols 0..K-1 = dW3^T),
 // 1 = X holds dZ2 (col 8 + O = db2), 2 = X holds dZ1 (cols 8..8+O-1 = dW1, col 8 + O = db1); jb = hidden units 128 jb ..
@@ -296,11 +304,15 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         return in;
     };
 
+    long long* ts_buf = (blockIdx.x == 0 && tid == 0) ? g_h256_ts : nullptr;
+    int tile_no = -1;
     RowIn nxt = gather(cta);
     bool pendingW = false;   // G4 of the previous tile still reads X / NB
     for (int tile = cta; tile < a.ntiles; tile += ncta) {
         const RowIn cur = nxt;
         nxt = gather(tile + ncta);
+        tile_no++;
+        H_TS(0);
         // ---- P1: h1 = tanh(P1 [x, 1]) for this thread's 64 hidden units, kept as packed 16-bit pairs
         float xe[OP];
 #pragma unroll
@@ -325,7 +337,9 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
 #pragma unroll
             for (int i = 0; i < 4; i++) h1p[c * 4 + i] = pack2<FMT>(h[2 * i], h[2 * i + 1]);
         }
+        H_TS(1);
         if (pendingW) { mbar_wait(doneW, pw); pw ^= 1u; }
+        H_TS(2);
 #pragma unroll
         for (int c = 0; c < 8; c++)
             *reinterpret_cast<uint4*>(Xq + act_chunk_off(wt, c)) =
@@ -338,10 +352,12 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         }
         fence_async_smem();
         mbar_arrive(ready);
+        H_TS(3);
 
         // ---- P2a: h2 = tanh(Z + b2) -> X (and registers); partial logits; the row's loss; dOut -> NB
         mbar_wait(doneZ, pz); pz ^= 1u;
         tc_fence_after();
+        H_TS(4);
         float lg[H_MAX_K];
 #pragma unroll
         for (int k = 0; k < H_MAX_K; k++) lg[k] = 0.0f;
@@ -378,7 +394,9 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
             for (int k = 0; k < H_MAX_K; k++)
                 if (k < k3) pp[k] = lg[k];
         }
+        H_TS(5);
         bar_sync(1, H_NCOMP);
+        H_TS(6);
         if (owner) {
 #pragma unroll
             for (int k = 0; k < H_MAX_K; k++) {
@@ -415,10 +433,12 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
             }
             st8<FMT>(NB + wt * 16, d8);
         }
+        H_TS(7);
         fence_async_smem();
         bar_sync(1, H_NCOMP);
         tc_fence_before();
         mbar_arrive(ready);
+        H_TS(8);
 
         // ---- P2b: dZ2 = (dOut W3) (1 - h2^2) -> X (over h2, once G5 has read it)
         uint32_t dzp[32];
@@ -451,7 +471,9 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
                 }
             }
         }
+        H_TS(9);
         mbar_wait(doneW, pw); pw ^= 1u;   // G5 has read X (h2) and NB
+        H_TS(10);
 #pragma unroll
         for (int c = 0; c < 8; c++)
             *reinterpret_cast<uint4*>(Xq + act_chunk_off(wt, c)) =
@@ -460,9 +482,11 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         mbar_arrive(ready);
 
         // ---- P4: dZ1 = Z (1 - h1^2) -> X (once G2 / G3b have read dZ2 and the dZ2 store has left X)
+        H_TS(11);
         mbar_wait(doneZ, pz); pz ^= 1u;
         mbar_wait(doneW, pw); pw ^= 1u;
         tc_fence_after();
+        H_TS(12);
 #pragma unroll
         for (int c = 0; c < 4; c++) {
             float v[16];
@@ -480,6 +504,7 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         tc_fence_before();
         fence_async_smem();
         mbar_arrive(ready);
+        H_TS(13);
         pendingW = true;
     }
     if (pendingW) { mbar_wait(doneW, pw); pw ^= 1u; }
@@ -723,3 +748,8 @@ int launch_update_h256(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st) {
 }
 
 }  // namespace ppo
+
+extern "C" int ppo_debug_h256_timeline(long long* d_ts) {
+    PPO_CUDA(cudaMemcpyToSymbol(ppo::g_h256_ts, &d_ts, sizeof(d_ts)));
+    return PPO_OK;
+}

@@ -998,14 +998,22 @@ extern "C" int ppo_debug_tc_timeline(long long* d_ts, int who) {
     return PPO_OK;
 }
 namespace ppo {
-bool update_tc_supported(const Dims& d) {
-    return d.H == TC_H && d.O + 1 <= 8 && d.K <= TC_MAX_K && (size_t)tc_layout(d.K, 2).end + 1024 <= 227 * 1024;
-}
+static bool tc_fits(int K, int nwg) { return (size_t)tc_layout(K, nwg).end + 1024 <= 227 * 1024; }
+bool update_tc_supported(const Dims& d) { return d.H == TC_H && d.O + 1 <= 8 && d.K <= TC_MAX_K && tc_fits(d.K, 1); }
 int launch_update_tc(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st, const FuseAdam* fuse, float* grads_out,
                      float* diag_out, bool* tail_done) {
     if (tail_done) *tail_done = false;
     if (!update_tc_supported(a.d)) return PPO_ERR_UNSUPPORTED;
     const bool wide = a.d.O + 1 > 4;
+    // two compute warpgroups per CTA when their per-row logit scratch fits next to the activation tiles (K <= ~16),
+    // else one (the 21-logit MultiDiscrete shape nvec {3,3,3,3,3,2,2,2})
+    if (!tc_fits(a.d.K, 2)) {
+        if (fmt == FMT_BF16)
+            return wide ? launch_tc<FMT_BF16, 1, true>(a, grid_out, st, fuse, grads_out, diag_out, tail_done)
+                        : launch_tc<FMT_BF16, 1, false>(a, grid_out, st, fuse, grads_out, diag_out, tail_done);
+        return wide ? launch_tc<FMT_F16, 1, true>(a, grid_out, st, fuse, grads_out, diag_out, tail_done)
+                    : launch_tc<FMT_F16, 1, false>(a, grid_out, st, fuse, grads_out, diag_out, tail_done);
+    }
     if (fmt == FMT_BF16)
         return wide ? launch_tc<FMT_BF16, 2, true>(a, grid_out, st, fuse, grads_out, diag_out, tail_done)
                     : launch_tc<FMT_BF16, 2, false>(a, grid_out, st, fuse, grads_out, diag_out, tail_done);

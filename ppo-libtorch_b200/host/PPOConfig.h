@@ -14,6 +14,7 @@
 #include <sstream>
 #include <stdexcept>
 #include <string>
+#include <vector>
 
 namespace ppo_host {
 
@@ -48,6 +49,7 @@ struct Config {
     // [b200] (new, optional)
     std::string env;                 // "" = the trainer class's own env ("cartpole" | "mountaincar")
     int64_t hidden = 64;             // PPO/Agent.cpp:25-37 hard-codes 64
+    std::vector<int64_t> nvec;       // MultiDiscrete action space (PPO/Agent.cpp:16 keeps { 3,3,3,3,3,2,2,2 } commented); empty = { action_size }
     bool use_cuda_graph = true;
     bool exact_entropy = false;      // false = reproduce Distributions/Categorical.cpp:114-117
     // derived (:246-247)
@@ -83,7 +85,8 @@ inline std::string strip_comment(const std::string& s) {
     return s;
 }
 struct Value {
-    enum Kind { INT, FLOAT, BOOL, STRING } kind;
+    enum Kind { INT, FLOAT, BOOL, STRING, INT_ARRAY } kind;
+    std::vector<int64_t> arr;   // INT_ARRAY: [3, 3, 2]
     int64_t i = 0;
     double f = 0.0;
     bool b = false;
@@ -93,6 +96,21 @@ inline Value parse_value(const std::string& raw) {
     Value v;
     if (raw.empty()) throw std::runtime_error("missing value");
     if (raw == "true" || raw == "false") { v.kind = Value::BOOL; v.b = raw == "true"; return v; }
+    if (raw[0] == '[') {   // one-line array of integers (the only array the [b200] table uses: nvec)
+        if (raw.back() != ']') throw std::runtime_error("bad array " + raw);
+        v.kind = Value::INT_ARRAY;
+        std::string item;
+        std::istringstream ss(raw.substr(1, raw.size() - 2));
+        while (std::getline(ss, item, ',')) {
+            item = trim(item);
+            if (item.empty()) continue;
+            char* e = nullptr;
+            const long long x = std::strtoll(item.c_str(), &e, 0);
+            if (e == item.c_str() || *e != '\0') throw std::runtime_error("bad array element '" + item + "'");
+            v.arr.push_back(x);
+        }
+        return v;
+    }
     if (raw[0] == '"' || raw[0] == '\'') {
         if (raw.size() < 2 || raw.back() != raw[0]) throw std::runtime_error("bad string " + raw);
         v.kind = Value::STRING;
@@ -199,6 +217,7 @@ inline int load_config(const std::string& path, Config& c, std::ostream& log = s
     getf("ppo.max_grad_norm", c.max_grad_norm);
     gets("b200.env", c.env);
     geti("b200.hidden", c.hidden);
+    { auto it = kv.find("b200.nvec"); if (it != kv.end() && it->second.kind == V::INT_ARRAY) c.nvec = it->second.arr; }
     getb("b200.use_cuda_graph", c.use_cuda_graph);
     getb("b200.exact_entropy", c.exact_entropy);
     c.derive();

@@ -48,10 +48,21 @@ void PPOTrainerBase::build() {
     if (ppo_env_state_dim(kind) != m_obs_size)   // initEnvs' size check (PPO_Discrete.cpp:370-375)
         throw std::runtime_error("obs_size " + std::to_string(m_obs_size) + " does not match the environment's observation (" +
                                  std::to_string(ppo_env_state_dim(kind)) + " floats)");
-    m_shell = checkpoint_shell_create(m_obs_size, m_config.hidden, m_action_size, m_learning_rate, m_seed);
+    // action space: one head of action_size logits (Agent.cpp:21) unless PPO_MultiDiscrete is given the
+    // MultiDiscrete nvec the reference keeps commented at Agent.cpp:16 through `[b200] nvec = [..]`
+    std::vector<int64_t> nvec = {m_action_size};
+    if (m_multidiscrete && !m_config.nvec.empty()) nvec = m_config.nvec;
+    if (nvec.size() > PPO_MAX_HEADS) throw std::runtime_error("[b200] nvec: at most " + std::to_string(PPO_MAX_HEADS) + " heads");
+    int64_t sumK = 0;
+    for (int64_t k : nvec) {
+        if (k < 1) throw std::runtime_error("[b200] nvec: every head needs at least one logit");
+        sumK += k;
+    }
+    m_shell = checkpoint_shell_create(m_obs_size, m_config.hidden, sumK, m_learning_rate, m_seed);
     ppo_trainer_cfg c{};
-    c.dims.obs_dim = (int32_t)m_obs_size; c.dims.hidden = (int32_t)m_config.hidden; c.dims.heads = 1;
-    c.dims.nvec[0] = (int32_t)m_action_size;           // Agent.cpp:21: one head of action_size logits
+    c.dims.obs_dim = (int32_t)m_obs_size; c.dims.hidden = (int32_t)m_config.hidden; c.dims.heads = (int32_t)nvec.size();
+    for (size_t h = 0; h < nvec.size(); h++) c.dims.nvec[h] = (int32_t)nvec[h];
+    m_env_kind = kind;
     c.env_kind = kind; c.num_envs = (int32_t)m_num_envs; c.num_steps = (int32_t)m_num_steps;
     c.num_minibatches = (int32_t)m_num_minibatches; c.update_epochs = (int32_t)m_update_epochs;
     c.max_episode_steps = (int32_t)m_max_episode_steps; c.use_gae = m_use_gae; c.gamma = m_gamma; c.gae_lambda = m_gae_lambda;

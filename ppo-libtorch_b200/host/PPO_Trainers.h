@@ -37,7 +37,10 @@ public:
     // one PPO update (rollout + GAE + all optimiser steps) at learning rate lr; what train() loops over
     ppo_iter_result iterate(float lr);
     std::vector<float> getParameters() const;          // flat slab, reference registration order
-    ppo_trainer* handle() { return m_b200; }
+    ppo_trainer* handle() const { return m_b200; }
+    bool multidiscrete() const { return m_multidiscrete; }
+    void* stream() const { return m_stream; }
+    int envKind() const { return m_env_kind; }
 
     // Hyperparameters (PPO/PPO_Discrete.h:51-76)
     int64_t m_obs_size, m_action_size;
@@ -65,6 +68,7 @@ protected:
 
 private:
     bool m_multidiscrete;
+    int m_env_kind = 0;
     std::string m_config_path;
     ppo_trainer* m_b200 = nullptr;
     ppo_host::CheckpointShell* m_shell = nullptr;
@@ -73,11 +77,4 @@ private:
     template <typename T> void printElement(T t, int width);
 };
 
-class PPO_Discrete : public PPOTrainerBase {
-public:
-    explicit PPO_Discrete(const std::string& config_path = "./PPOConfig.toml") : PPOTrainerBase(false, config_path) { build(); }
-};
-class PPO_MultiDiscrete : public PPOTrainerBase {
-public:
-    explicit PPO_MultiDiscrete(const std::string& config_path = "./PPOConfig.toml") : PPOTrainerBase(true, config_path) { build(); }
-};
+// class PPO_Discrete / class PPO_MultiDiscrete: PPO_Discrete.h / PPO_MultiDiscrete.h (they add the tensor-level surface)

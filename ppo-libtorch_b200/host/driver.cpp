@@ -3,7 +3,7 @@
 #include <cstring>
 #include <iostream>
 
-#include "PPO_Trainers.h"
+#include "PPO_MultiDiscrete.h"
 
 int main(int argc, char** argv) {
     try {

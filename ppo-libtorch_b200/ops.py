@@ -86,6 +86,17 @@ def categorical(logits, nvec, mask=None, actions=None, uniforms=None, seed=0, co
 
 
 # ---- actor-critic (K1) ----------------------------------------------------------------------------
+def categorical_normalize(logits, nvec, mask=None):
+    """(m_logits, m_probs) of the distribution classes: x' - logsumexp(x') and softmax(x') per head"""
+    _cuda_required()
+    n, K = logits.shape
+    assert K == sum(nvec)
+    nv = (C.c_int32 * len(nvec))(*nvec)
+    ln, pr = torch.empty_like(logits), torch.empty_like(logits)
+    check(load().ppo_categorical_normalize(n, len(nvec), nv, ptr(logits), ptr(mask), ptr(ln), ptr(pr), stream_ptr()))
+    return ln, pr
+
+
 def policy_forward(params, obs_dim, hidden, nvec, obs, mask=None, actions=None, uniforms=None, seed=0, counter=0,
                    entropy_mode=capi.ENTROPY_REFERENCE, want_logits=False):
     """Agent::getActionAndValueDiscrete / getActionAndValueMasked -> (action, logprob, entropy, value[, logits])."""
@@ -182,6 +193,19 @@ def adv_partials(adv, mb_size, n_mb, perm=None):
     check(load().ppo_adv_stats(ptr(adv), ptr(perm), adv.numel(), mb_size, n_mb, None, ptr(out),
                                ptr(_adv_workspace(n_mb, adv.device)), stream_ptr()))
     return out
+
+
+def adv_stats_all_epochs(adv, mb_size, n_mb, n_epochs, seed, epoch0=0):
+    """statistics of all n_epochs x n_mb minibatches of an update through the keyed permutation (perm_index of
+    make_permutation(batch, seed, epoch0 + e)) -> (float32 [n_epochs * n_mb, 2], float64 [n_epochs * n_mb, 3])"""
+    _cuda_required()
+    n_all = n_mb * n_epochs
+    out = torch.empty((n_all, 2), dtype=torch.float32, device=adv.device)
+    part = torch.empty((n_all, 3), dtype=torch.float64, device=adv.device)
+    ws = _adv_workspace(n_all, adv.device)
+    check(load().ppo_adv_stats_all_epochs(ptr(adv), adv.numel(), mb_size, n_mb, n_epochs, seed, epoch0, None, ptr(out),
+                                          ptr(part), ptr(ws), stream_ptr()))
+    return out, part
 
 
 def adv_stats_finalize(partials):

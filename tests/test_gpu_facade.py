@@ -163,3 +163,34 @@ def test_multidiscrete_driver_mountaincar(exe, tmp_path):
     mod = torch.jit.load(str(tmp_path / "Models" / f"PPO_Agent_{3 * BATCH}_steps.pt"), map_location="cpu")
     shapes = {k: tuple(v.shape) for k, v in mod.named_parameters()}
     assert shapes["m_Actor.actorOutputLayer.weight"] == (3, 64) and shapes["m_Critic.criticInputLayer.weight"] == (64, 2)
+
+
+# --------------------------------------------------------------------------- the reference's class surface in C++
+API_CHECK = os.path.join(ROOT, "ppo-libtorch_b200", "ppo_api_check")
+REF_DRIVER = os.path.join(ROOT, "ppo-libtorch_b200", "ppo_ref_driver_on_b200")
+
+
+def test_cpp_class_surface_against_libtorch(tmp_path):
+    """host/api_check.cpp: Agent / Categorical / CategoricalMasked (every public method and member of
+    PPO/Agent.h:30-54, Distributions/*.h) against LibTorch's own Sequential::forward / log_softmax / gather on the same
+    tensors, then PPO_Discrete's computeActionLogic / calcAdvantage / getApproxKLAndClippedObj / initEnvs / stepEnvs and
+    the m_obs .. m_values views (PPO/PPO_Discrete.h:35-43,88-94)."""
+    assert os.path.exists(API_CHECK), "ppo-libtorch_b200/ppo_api_check is not built"
+    with open(tmp_path / "PPOConfig.toml", "w") as f:
+        f.write(TOML.format(total=4 * BATCH, cuda="true"))
+    p = subprocess.run([API_CHECK, "trainer"], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0 and "api_check: all ok" in p.stdout, p.stdout[-3000:] + p.stderr[-2000:]
+    for what in ("Agent.getValue = m_Critic->forward (LibTorch)", "Categorical.entropy (reference quirk)",
+                 "CategoricalMasked.sample never picks a masked action", "PPO_Discrete.stepEnvs returns",
+                 "PPO_Discrete.calcAdvantage", "PPO_Discrete.m_agent parameters alias the trainer's slab"):
+        assert "ok " + what in p.stdout, what
+
+
+def test_reference_driver_source_runs_on_the_facade(tmp_path):
+    """ppo_ref_driver_on_b200 = the reference's OWN driver.cpp (compiled unmodified with -Ihost/compat, host/Makefile)
+    linked against this facade: `PPO_Discrete algo; algo.train();` trains on the GPU and prints the reference's table."""
+    if not os.path.exists(REF_DRIVER):
+        pytest.skip("built only where /root/reference exists (travels with the snapshot)")
+    out = run(REF_DRIVER, str(tmp_path), 3 * BATCH, True)
+    assert out.count("|    total_timesteps      | ") == 2 and "Error Occured" not in out
+    assert (tmp_path / "Models" / f"PPO_Agent_{3 * BATCH}_steps.pt").exists()

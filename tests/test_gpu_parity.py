@@ -438,6 +438,34 @@ def test_permutation_is_bijection(P, batch):
         assert (p.long() == torch.arange(batch, device="cuda")).float().mean().item() < 0.01
 
 
+@pytest.mark.parametrize("batch,n_mb", [(1 << 23, 4), ((1 << 22) + 12345, 4), ((1 << 22) + 7, 3)])
+def test_adv_stats_all_epochs_coalesced_equals_gather(P, request, batch, n_mb):
+    """the one-coalesced-pass-per-epoch kernel (inverse permutation, >= 2^22 rows) against the permuted-gather kernel and
+    against the materialised permutation: same minibatch membership, sums equal to double rounding"""
+    lib = P.capi.load()
+    request.addfinalizer(lambda: lib.ppo_debug_adv_impl(1))
+    rng = np.random.default_rng(batch % 1000)
+    adv = dev((rng.standard_normal(batch) * 2 + 0.3).astype(np.float32))
+    E, seed = 3, 77
+    mb_size = batch // n_mb
+    n_eff = (batch + mb_size - 1) // mb_size
+    lib.ppo_debug_adv_impl(1)
+    s1, p1 = P.ops.adv_stats_all_epochs(adv, mb_size, n_eff, E, seed, epoch0=5)
+    lib.ppo_debug_adv_impl(0)
+    s0, p0 = P.ops.adv_stats_all_epochs(adv, mb_size, n_eff, E, seed, epoch0=5)
+    assert torch.equal(p1[:, 0], p0[:, 0])                                      # same row counts
+    # sums: fp32 partial sums of 32 rows flushed into double accumulators against all-double sums
+    np.testing.assert_allclose(p1.cpu().numpy(), p0.cpu().numpy(), rtol=2e-6, atol=1e-2)
+    np.testing.assert_allclose(s1.cpu().numpy(), s0.cpu().numpy(), rtol=2e-6, atol=2e-6)
+    perm = P.ops.make_permutation(batch, seed, 6).long()                        # epoch 1 of the call above
+    x = adv[perm[mb_size:2 * mb_size]].double()
+    np.testing.assert_allclose(s1[n_eff + 1].cpu().numpy(), [x.mean().item(), x.std(unbiased=True).item()], rtol=1e-5)
+    s1b, _ = P.ops.adv_stats_all_epochs(adv, mb_size, n_eff, E, seed, epoch0=5)  # workspace left clean, deterministic
+    lib.ppo_debug_adv_impl(1)
+    s1c, _ = P.ops.adv_stats_all_epochs(adv, mb_size, n_eff, E, seed, epoch0=5)
+    assert torch.equal(torch.nan_to_num(s1c, nan=-7.0), torch.nan_to_num(s1, nan=-7.0))   # a 1-row minibatch has std NaN
+
+
 # ---------------------------------------------------------------------------------------------- rollout
 @pytest.mark.parametrize("kind,O,nvec,masked,H,n,T", [(0, 4, [2], False, 64, 100, 24), (0, 4, [1], False, 64, 8, 32),
                                                       (1, 2, [3], True, 64, 77, 20), (1, 2, [3], False, 256, 40, 6),

@@ -163,3 +163,26 @@ def test_abi_version_matches_header():
     hdr = open(os.path.join(root, "include", "ppo_b200.h")).read()
     v = int(re.search(r"#define\s+PPO_B200_ABI_VERSION\s+(\d+)", hdr).group(1))
     assert v == P.capi.ABI_VERSION == P.capi.load().ppo_abi_version()
+
+
+def test_library_exports_every_declared_symbol():
+    """every function include/*.h declares (the drop-in ABI and the diagnostics header) is exported by libppo_b200.so
+    or, for the host facade's C entry points, libppo_host.so — checked with nm-style symbol lookup, no compute call"""
+    import ctypes
+    import glob
+    import re
+    import ppo_libtorch_b200 as P
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = P.capi.load()
+    names = set()
+    for h in glob.glob(os.path.join(root, "include", "*.h")):
+        txt = re.sub(r"/\*.*?\*/", "", open(h).read(), flags=re.S)
+        names |= set(re.findall(r"\b(ppo_[a-z0-9_]+)\s*\(", txt))
+    assert len(names) > 40
+    missing = []
+    for n in sorted(names):
+        try:
+            getattr(lib, n)
+        except AttributeError:
+            missing.append(n)
+    assert not missing, f"declared but not exported: {missing}"
