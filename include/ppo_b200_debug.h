@@ -51,6 +51,7 @@ int ppo_debug_adv_impl(int impl);
  * SM clock of CTA 0 / thread 0 at 14 phase edges of its first 4 tiles, 16 slots per tile (tools/h256_timeline.py). */
 int ppo_debug_h256_timeline(long long* d_ts);
 
+
 #ifdef __cplusplus
 }
 #endif

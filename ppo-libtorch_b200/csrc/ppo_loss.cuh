@@ -145,4 +145,62 @@ __device__ inline void actor_row_loss_fast1(float* x, int K, int aa, float old_l
     }
 }
 
+
+// actor_row_loss_fast1 with the row held in registers (KMAX = compile-time bound of K, loops fully unrolled and predicated):
+// one exponential per logit, reused for the probabilities of the backward pass; no shared-memory round trips inside the
+// dependent chain.  x[0..K) = logits on entry, dL/dlogits on exit.  Same formulas and the same intrinsics.
+template <int KMAX>
+__device__ __forceinline__ void actor_row_loss_fast_reg(float (&x)[KMAX], int K, int aa, float old_logp, float adv_raw,
+                                                        const ppo_hyper& hp, float meanf, float rstd, RowSumsF& s) {
+    const float c = hp.clip_coef, lo = 1.0f - c, hi = 1.0f + c;
+    float mx = x[0];
+#pragma unroll
+    for (int j = 1; j < KMAX; j++)
+        if (j < K) mx = fmaxf(mx, x[j]);
+    float e[KMAX], sum = 0.0f, xa = x[0];
+#pragma unroll
+    for (int j = 0; j < KMAX; j++) {
+        e[j] = j < K ? __expf(x[j] - mx) : 0.0f;
+        sum += e[j];
+        if (j == aa) xa = x[j];
+    }
+    const float lse = mx + __logf(sum), rs = __fdividef(1.0f, sum);
+    const float newlogp = xa - lse;
+    const bool exact = hp.entropy_mode == PPO_ENTROPY_EXACT;
+    float ent = 0.0f;
+    if (exact) {
+#pragma unroll
+        for (int j = 0; j < KMAX; j++) {
+            const float p = e[j] * rs;
+            if (j < K && p > 0.0f) ent -= (x[j] - lse) * p;
+        }
+    } else {
+        ent = -FLT_MIN;   // Categorical.cpp:114-117
+    }
+    const float logratio = newlogp - old_logp;
+    const float ratio = __expf(logratio);
+    s.kl += (ratio - 1.0f) - logratio;
+    if (fabsf(ratio - 1.0f) > c) s.clip += 1.0f;
+    float A = adv_raw;
+    if (hp.norm_adv) A = (A - meanf) * rstd;     // rstd = 1 / (std + 1e-8), formed once per kernel with __fdividef
+    const float rc = ratio < lo ? lo : (ratio > hi ? hi : ratio);
+    const float pg1 = -A * ratio, pg2 = -A * rc;
+    s.pg += pg1 > pg2 ? pg1 : pg2;
+    s.ent += ent;
+    float dpg_dr;
+    if (ratio >= lo && ratio <= hi) dpg_dr = -A;
+    else if (pg1 > pg2) dpg_dr = -A;
+    else if (pg1 == pg2) dpg_dr = -0.5f * A;
+    else dpg_dr = 0.0f;
+    const float g_logp = dpg_dr * ratio;
+    const float ge = hp.ent_coef;
+#pragma unroll
+    for (int j = 0; j < KMAX; j++) {
+        const float p = e[j] * rs;
+        float dz = g_logp * ((j == aa ? 1.0f : 0.0f) - p);
+        if (exact && ge != 0.0f && p > 0.0f) dz += ge * p * ((x[j] - lse) + ent);
+        x[j] = j < K ? dz : 0.0f;
+    }
+}
+
 }  // namespace ppo

@@ -37,7 +37,7 @@ using namespace umma;
 
 
 struct HLayout {   // byte offsets into the 1024-aligned dynamic shared memory of update_h256_kernel
-    int w2, x, nb, p1, b2, w3, b3, part, doutf, gb, bars, tmem_slot, end;
+    int w2, x, nb, p1, b2, w3, b3, part, doutf, gb, w3h, bars, tmem_slot, end;
     int op, ldp;   // floats per P1 row (4 or 8), logits row stride
 };
 __host__ __device__ inline HLayout h_layout(int O, int K) {
@@ -58,6 +58,11 @@ __host__ __device__ inline HLayout h_layout(int O, int K) {
     o = (o + 15) & ~15;
     L.bars = o; o += 8 * 8;
     L.tmem_slot = o; o += 16;
+    // 16-bit W3^T as a K-major narrow tile [2 chunks][256 units][16 B] (chunk 0 = W3[0..8)[j], chunk 1 = 0): B operand of
+    // G6, dh2 = dOut W3 on the tensor core.  Only when it fits (-1: P2b forms dh2 with FMAs against the fp32 W3 instead).
+    o = (o + 127) & ~127;
+    L.w3h = -1;
+    if ((size_t)o + 2 * HH * 16 + 1024 <= 227 * 1024) { L.w3h = o; o += 2 * HH * 16; }
     L.end = o;
     return L;
 }
@@ -134,6 +139,11 @@ __device__ __forceinline__ void h256_issuer(const H256Args& a, const CUtensorMap
                     mma_f16(tmem + h_acc_col(0, jb), mn_desc(X + (uint32_t)jb * 2u * H_PANEL_X, H_PANEL_X, ks),
                             narrow_desc_mnmajor(NB, HR, ks), id_sm, ks > 0 ? 1u : (first ^ 1u));
             mma_commit(doneW);
+            if (L.w3h >= 0) {   // G6: Z = NB W3h^T = dOut W3 (K = 16: the {x, 1} chunk meets the zero chunk of W3h)
+                mma_f16(tmem, narrow_desc_kmajor(NB, HR * 16), narrow_desc_kmajor(sb + (uint32_t)L.w3h, HH * 16), id_fwd, 0u);
+                mma_commit(doneZ);
+                mbar_arrive(doneZ);   // doneZ counts two arrivals per phase (the other phases pair the commit with a TMA store)
+            }
         }
         __syncwarp();
         // ---- P2b staged: X = dZ2.  dZ2 -> scratch, G2 (dX), G3b (db2)
@@ -180,8 +190,13 @@ __device__ __forceinline__ void h256_issuer(const H256Args& a, const CUtensorMap
 }
 
 // ---- the fused forward / loss / backward kernel ------------------------------------------------------------------------------
-template <int FMT, int OP>
-__global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a, const __grid_constant__ CUtensorMap tmap) {
+// NQ = compute warpgroups (2 or 4): a thread owns row wt of the tile x CPT = 256 / NQ hidden units.  NQ = 4: 16 compute
+// warps of 112 registers; NQ = 2: 8 compute warps of 232 registers (room for the compiler to keep whole 16-column groups
+// of loads in flight).  ppo_debug_h256_variant picks; the default is what measured faster on B200.
+template <int FMT, int OP, int NQ, int KMAX>
+__global__ void __launch_bounds__(128 * (NQ + 1), 1)
+    update_h256_kernel(const H256Args a, const __grid_constant__ CUtensorMap tmap) {
+    constexpr int NCOMP = 128 * NQ, NTHR = 128 * (NQ + 1), CPT = HH / NQ, NCH = CPT / 8, PPT = CPT / 64;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const UpdArgs& u = a.u;
@@ -191,23 +206,24 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
     const int net = (int)blockIdx.x & 1;                // 0 = actor, 1 = critic
     const int k3 = net == 0 ? K : 1;
     const NetOff of = net == 0 ? actor_off(O, HH, K) : critic_off(O, HH);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + L.bars);   // ready (512 arrivals), doneZ (2), doneW (1)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + L.bars);   // ready (NCOMP arrivals), doneZ (2), doneW (1)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + L.tmem_slot);
     const int cta = (int)blockIdx.x >> 1, ncta = (int)gridDim.x >> 1;
+    const bool dh_mma = L.w3h >= 0;
 
     // ---------------- prologue: tensor memory, barriers, this net's parameters -> shared memory ----------------
     if (warp == 0) tmem_alloc(tmem_slot, 512);
     if (tid == 0) {
-        mbar_init(bars + 0, H_NCOMP);
+        mbar_init(bars + 0, NCOMP);
         mbar_init(bars + 1, 2);
         mbar_init(bars + 2, 1);
         mbar_init_fence();
     }
-    if (warp == 16 && lane == 0) tma::prefetch_map(&tmap);
-    stage_w2_panels<FMT>(sm + L.w2, u.params + of.W2, tid, H_NTHR);
+    if (warp == 4 * NQ && lane == 0) tma::prefetch_map(&tmap);
+    stage_w2_panels<FMT>(sm + L.w2, u.params + of.W2, tid, NTHR);
     {
         float* P1 = reinterpret_cast<float*>(sm + L.p1);
-        for (int e = tid; e < HH * OP; e += H_NTHR) {   // P1[j] = {W1[j][0..O), b1[j], 0..}
+        for (int e = tid; e < HH * OP; e += NTHR) {   // P1[j] = {W1[j][0..O), b1[j], 0..}
             const int j = e / OP, i = e - j * OP;
             float v = 0.0f;
             if (i < O) v = __ldg(u.params + of.W1 + j * O + i);
@@ -215,11 +231,23 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
             P1[e] = v;
         }
         float* B2 = reinterpret_cast<float*>(sm + L.b2);
-        for (int e = tid; e < HH; e += H_NTHR) B2[e] = __ldg(u.params + of.b2 + e);
+        for (int e = tid; e < HH; e += NTHR) B2[e] = __ldg(u.params + of.b2 + e);
         float* W3 = reinterpret_cast<float*>(sm + L.w3);
-        for (int e = tid; e < k3 * HH; e += H_NTHR) W3[e] = __ldg(u.params + of.W3 + e);
+        for (int e = tid; e < k3 * HH; e += NTHR) W3[e] = __ldg(u.params + of.W3 + e);
         float* B3 = reinterpret_cast<float*>(sm + L.b3);
         if (tid < 8) B3[tid] = tid < k3 ? __ldg(u.params + of.b3 + tid) : 0.0f;
+        if (dh_mma) {   // W3h: unit j's 16-byte chunk = {W3[0][j] .. W3[7][j]} in 16 bits, then a chunk of zeros
+            for (int j = tid; j < HH; j += NTHR) {
+                float v[8], z[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    v[k] = k < k3 ? __ldg(u.params + of.W3 + k * HH + j) : 0.0f;
+                    z[k] = 0.0f;
+                }
+                st8<FMT>(sm + L.w3h + j * 16, v);
+                st8<FMT>(sm + L.w3h + HH * 16 + j * 16, z);
+            }
+        }
     }
     fence_async_smem();
     tc_fence_before();
@@ -227,27 +255,29 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    if (warp >= 16) {   // control warpgroup: warp 16 issues every MMA and TMA store, the others only give up registers
+    if (warp >= 4 * NQ) {   // control warpgroup: its first warp issues every MMA and TMA store, the others only give up registers
         asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
-        if (warp == 16) h256_issuer<FMT>(a, &tmap, L, sm, bars, tmem, net, lane);
+        if (warp == 4 * NQ) h256_issuer<FMT>(a, &tmap, L, sm, bars, tmem, net, lane);
         return;
     }
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+    // registers released by the control warpgroup must cover the request (the pool is the CTA's launch allocation)
+    if constexpr (NQ == 4) asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+    else asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
 
-    // ---------------- compute threads: row wt of the tile x hidden units 64 q .. 64 q + 63 (= panel q of X) -----------
+    // ---------------- compute threads: row wt of the tile x hidden units CPT q .. CPT q + CPT - 1 -----------------------
     const int wt = tid & 127, q = warp >> 2, w4 = warp & 3;
     const bool owner = q == 0;               // runs the per-row loss and owns the row's scalar inputs
     uint64_t *ready = bars, *doneZ = bars + 1, *doneW = bars + 2;
     uint32_t pz = 0u, pw = 0u;
-    uint8_t* Xq = sm + L.x + q * H_PANEL_X;
+    uint8_t* X0 = sm + L.x + q * PPT * H_PANEL_X;      // this thread's PPT panels of X; chunk c at panel c / 8, chunk c % 8
     uint8_t* NB = sm + L.nb;
-    const float* P1 = reinterpret_cast<const float*>(sm + L.p1) + (q * 64) * OP;
-    const float* B2 = reinterpret_cast<const float*>(sm + L.b2) + q * 64;
-    const float* W3 = reinterpret_cast<const float*>(sm + L.w3) + q * 64;
+    const float* P1 = reinterpret_cast<const float*>(sm + L.p1) + (q * CPT) * OP;
+    const float* B2 = reinterpret_cast<const float*>(sm + L.b2) + q * CPT;
+    const float* W3 = reinterpret_cast<const float*>(sm + L.w3) + q * CPT;
     const float* B3 = reinterpret_cast<const float*>(sm + L.b3);
     float* part = reinterpret_cast<float*>(sm + L.part);
     float* xrow = reinterpret_cast<float*>(sm + L.doutf) + wt * L.ldp;   // this row's logits -> dL/dlogits
-    const uint32_t zaddr = tmem_addr(tmem, (uint32_t)w4 * 32u, (uint32_t)q * 64u);
+    const uint32_t zaddr = tmem_addr(tmem, (uint32_t)w4 * 32u, (uint32_t)(q * CPT));
     const bool masked = u.mask != nullptr;
     float meanf = 0.0f, stdf = 1.0f;
     if (u.hp.norm_adv) { meanf = u.adv_stats[0]; stdf = u.adv_stats[1]; }
@@ -255,12 +285,13 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
     float* gbrow = reinterpret_cast<float*>(sm + L.gb) + wt;   // [k][128]: this row slot's running sum of dOut[k]
     if (owner)
         for (int k = 0; k < k3; k++) gbrow[k * HR] = 0.0f;
+    auto xchunk = [&](int c) -> uint8_t* { return X0 + (c >> 3) * H_PANEL_X + act_chunk_off(wt, c & 7); };
 
+    // the observation of the NEXT tile's row is gathered one tile ahead (P1 needs it at once); the loss inputs of a row are
+    // loaded by its owner thread at the top of the tile and are not needed before the loss, ~10 k cycles later
     struct RowIn {
         int64_t r;
         float o[4];
-        float old_logp, adv, ret, old_val;
-        int act0;
         bool on;
     };
     uint32_t pkey[4] = {0u, 0u, 0u, 0u};
@@ -271,8 +302,6 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         in.on = tile < a.ntiles && rloc < u.mb_size;
         in.r = 0;
         in.o[0] = in.o[1] = in.o[2] = in.o[3] = 0.0f;
-        in.old_logp = in.adv = in.ret = in.old_val = 0.0f;
-        in.act0 = 0;
         if (in.on) {
             const int64_t r = u.perm ? (int64_t)__ldg(u.perm + u.mb_start + rloc)
                                      : (u.pf.inline_on ? perm_index(u.mb_start + rloc, u.pf.batch, u.pf.half_bits, pkey)
@@ -281,28 +310,15 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
             if (u.rec) {   // packed row: {obs[4]} {old_logp, adv, ret, old_val} {action, -, -, -} {-}
                 const float4 q0 = __ldg(u.rec + r * 4);
                 in.o[0] = q0.x; in.o[1] = q0.y; in.o[2] = q0.z; in.o[3] = q0.w;
-                if (owner) {
-                    const float4 q1 = __ldg(u.rec + r * 4 + 1), q2 = __ldg(u.rec + r * 4 + 2);
-                    in.old_logp = q1.x; in.adv = q1.y; in.ret = q1.z; in.old_val = q1.w;
-                    in.act0 = __float_as_int(q2.x);
-                }
-                return in;
-            }
-            if (O <= 4) {
+            } else if (O <= 4) {
 #pragma unroll
                 for (int i = 0; i < 4; i++)
                     if (i < O) in.o[i] = __ldg(u.obs + r * O + i);
             }
-            if (owner) {
-                in.old_logp = __ldg(u.old_logprob + r);
-                in.act0 = __ldg(u.actions + r * heads);
-                in.adv = __ldg(u.adv + r);
-                in.ret = __ldg(u.ret + r);
-                if (u.hp.clip_vloss) in.old_val = __ldg(u.old_val + r);
-            }
         }
         return in;
     };
+    const float rstd = __fdividef(1.0f, stdf + 1e-8f);
 
     long long* ts_buf = (blockIdx.x == 0 && tid == 0) ? g_h256_ts : nullptr;
     int tile_no = -1;
@@ -313,7 +329,22 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         nxt = gather(tile + ncta);
         tile_no++;
         H_TS(0);
-        // ---- P1: h1 = tanh(P1 [x, 1]) for this thread's 64 hidden units, kept as packed 16-bit pairs
+        float c_old_logp = 0.0f, c_adv = 0.0f, c_ret = 0.0f, c_old_val = 0.0f;
+        int c_act0 = 0;
+        if (owner && cur.on) {
+            if (u.rec) {
+                const float4 q1 = __ldg(u.rec + cur.r * 4 + 1);
+                c_old_logp = q1.x; c_adv = q1.y; c_ret = q1.z; c_old_val = q1.w;
+                c_act0 = __float_as_int(__ldg(reinterpret_cast<const float*>(u.rec + cur.r * 4 + 2)));
+            } else {
+                c_old_logp = __ldg(u.old_logprob + cur.r);
+                c_act0 = __ldg(u.actions + cur.r * heads);
+                c_adv = __ldg(u.adv + cur.r);
+                c_ret = __ldg(u.ret + cur.r);
+                if (u.hp.clip_vloss) c_old_val = __ldg(u.old_val + cur.r);
+            }
+        }
+        // ---- P1: h1 = tanh(P1 [x, 1]) for this thread's hidden units, kept as packed 16-bit pairs
         float xe[OP];
 #pragma unroll
         for (int i = 0; i < OP; i++) xe[i] = 0.0f;
@@ -329,9 +360,9 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
 #pragma unroll
         for (int i = 0; i < OP; i++)
             if (i == O) xe[i] = 1.0f;
-        uint32_t h1p[32];
+        uint32_t h1p[CPT / 2];
 #pragma unroll
-        for (int c = 0; c < 8; c++) {
+        for (int c = 0; c < NCH; c++) {
             float h[8];
             layer1_8<OP>(P1 + c * 8 * OP, xe, h);
 #pragma unroll
@@ -341,9 +372,8 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         if (pendingW) { mbar_wait(doneW, pw); pw ^= 1u; }
         H_TS(2);
 #pragma unroll
-        for (int c = 0; c < 8; c++)
-            *reinterpret_cast<uint4*>(Xq + act_chunk_off(wt, c)) =
-                make_uint4(h1p[c * 4], h1p[c * 4 + 1], h1p[c * 4 + 2], h1p[c * 4 + 3]);
+        for (int c = 0; c < NCH; c++)
+            *reinterpret_cast<uint4*>(xchunk(c)) = make_uint4(h1p[c * 4], h1p[c * 4 + 1], h1p[c * 4 + 2], h1p[c * 4 + 3]);
         if (owner) {
             float x8[8];
 #pragma unroll
@@ -354,15 +384,15 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         mbar_arrive(ready);
         H_TS(3);
 
-        // ---- P2a: h2 = tanh(Z + b2) -> X (and registers); partial logits; the row's loss; dOut -> NB
+        // ---- P2a: h2 = tanh(Z + b2) -> X; partial logits; the row's loss; dOut -> NB
         mbar_wait(doneZ, pz); pz ^= 1u;
         tc_fence_after();
         H_TS(4);
-        float lg[H_MAX_K];
+        float lg[KMAX];
 #pragma unroll
-        for (int k = 0; k < H_MAX_K; k++) lg[k] = 0.0f;
+        for (int k = 0; k < KMAX; k++) lg[k] = 0.0f;
 #pragma unroll
-        for (int c = 0; c < 4; c++) {
+        for (int c = 0; c < CPT / 16; c++) {
             float v[16];
             tmem_ld16(zaddr + c * 16, v);
             tmem_ld_wait();
@@ -373,7 +403,7 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
                 v[i4 * 4 + 2] = tanh_fast256(v[i4 * 4 + 2] + b.z); v[i4 * 4 + 3] = tanh_fast256(v[i4 * 4 + 3] + b.w);
             }
 #pragma unroll
-            for (int k = 0; k < H_MAX_K; k++) {
+            for (int k = 0; k < KMAX; k++) {
                 if (k < k3) {
                     float s0 = 0.0f, s1 = 0.0f;
 #pragma unroll
@@ -385,74 +415,112 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
                     lg[k] += s0 + s1;
                 }
             }
-            st8<FMT>(Xq + act_chunk_off(wt, c * 2), v);          // h2 stays in X: G5 reads it, P2b re-reads it
-            st8<FMT>(Xq + act_chunk_off(wt, c * 2 + 1), v + 8);
+            st8<FMT>(xchunk(c * 2), v);          // h2 stays in X: G5 reads it, P2b re-reads it
+            st8<FMT>(xchunk(c * 2 + 1), v + 8);
         }
         {
             float* pp = part + (q * HR + wt) * L.ldp;
 #pragma unroll
-            for (int k = 0; k < H_MAX_K; k++)
+            for (int k = 0; k < KMAX; k++)
                 if (k < k3) pp[k] = lg[k];
         }
         H_TS(5);
-        bar_sync(1, H_NCOMP);
+        bar_sync(1, NCOMP);
         H_TS(6);
         if (owner) {
+            float xr[KMAX];
 #pragma unroll
-            for (int k = 0; k < H_MAX_K; k++) {
+            for (int k = 0; k < KMAX; k++) {
+                xr[k] = 0.0f;
                 if (k < k3) {
                     float s = B3[k];
 #pragma unroll
-                    for (int qq = 0; qq < 4; qq++) s += part[(qq * HR + wt) * L.ldp + k];
-                    xrow[k] = s;
+                    for (int qq = 0; qq < NQ; qq++) s += part[(qq * HR + wt) * L.ldp + k];
+                    xr[k] = s;
                 }
             }
             float d8[8];
 #pragma unroll
             for (int k = 0; k < 8; k++) d8[k] = 0.0f;
             if (net == 0) {
-                if (cur.on) {
-                    if (heads == 1 && !masked) {
-                        actor_row_loss_fast1(xrow, K, cur.act0, cur.old_logp, cur.adv, u.hp, meanf, stdf, rs);
-                    } else {
-                        const uint64_t mbits = masked ? pack_mask(u.mask + cur.r * K, K) : ~0ull;
-                        actor_row_loss(xrow, u.d, masked, mbits, u.actions + cur.r * heads, cur.old_logp, cur.adv, u.hp,
-                                       meanf, stdf, 1.0f, rs);
+                if (heads == 1 && !masked) {   // PPO_Discrete: the row stays in registers
+                    if (cur.on) actor_row_loss_fast_reg<KMAX>(xr, K, c_act0, c_old_logp, c_adv, u.hp, meanf, rstd, rs);
+                    else {
+#pragma unroll
+                        for (int k = 0; k < KMAX; k++) xr[k] = 0.0f;
                     }
                 } else {
-                    for (int k = 0; k < K; k++) xrow[k] = 0.0f;
+#pragma unroll
+                    for (int k = 0; k < KMAX; k++)
+                        if (k < K) xrow[k] = xr[k];
+                    if (cur.on) {
+                        const uint64_t mbits = masked ? pack_mask(u.mask + cur.r * K, K) : ~0ull;
+                        actor_row_loss(xrow, u.d, masked, mbits, u.actions + cur.r * heads, c_old_logp, c_adv, u.hp, meanf, stdf,
+                                       1.0f, rs);
+                    } else {
+                        for (int k = 0; k < K; k++) xrow[k] = 0.0f;
+                    }
+#pragma unroll
+                    for (int k = 0; k < KMAX; k++) xr[k] = k < K ? xrow[k] : 0.0f;
                 }
 #pragma unroll
-                for (int k = 0; k < H_MAX_K; k++)
-                    if (k < K) { d8[k] = xrow[k]; gbrow[k * HR] += d8[k]; }
+                for (int k = 0; k < KMAX; k++)
+                    if (k < K) { d8[k] = xr[k]; gbrow[k * HR] += xr[k]; }
             } else {
-                const float gv = cur.on ? critic_row_loss(xrow[0], cur.ret, cur.old_val, u.hp, 1.0f, rs) : 0.0f;
-                xrow[0] = gv;
+                const float gv = cur.on ? critic_row_loss(xr[0], c_ret, c_old_val, u.hp, 1.0f, rs) : 0.0f;
+                xr[0] = gv;
                 d8[0] = gv;
                 gbrow[0] += gv;
+            }
+            if (!dh_mma) {   // P2b's FMA path reads dL/dlogits of the row from shared memory
+#pragma unroll
+                for (int k = 0; k < KMAX; k++)
+                    if (k < k3) xrow[k] = xr[k];
             }
             st8<FMT>(NB + wt * 16, d8);
         }
         H_TS(7);
         fence_async_smem();
-        bar_sync(1, H_NCOMP);
+        bar_sync(1, NCOMP);
         tc_fence_before();
         mbar_arrive(ready);
         H_TS(8);
 
         // ---- P2b: dZ2 = (dOut W3) (1 - h2^2) -> X (over h2, once G5 has read it)
-        uint32_t dzp[32];
-        {
-            float dq[H_MAX_K];
+        uint32_t dzp[CPT / 2];
+        if (dh_mma) {
+            // dOut W3 comes from the tensor core (G6, issued behind G5): this thread only applies the tanh derivative
+            mbar_wait(doneZ, pz); pz ^= 1u;
+            tc_fence_after();
 #pragma unroll
-            for (int k = 0; k < H_MAX_K; k++) dq[k] = k < k3 ? xrow[k] : 0.0f;
+            for (int c = 0; c < CPT / 16; c++) {
+                float v[16];
+                tmem_ld16(zaddr + c * 16, v);
+                tmem_ld_wait();
 #pragma unroll
-            for (int c = 0; c < 8; c++) {
+                for (int hc = 0; hc < 2; hc++) {
+                    const uint4 hq = *reinterpret_cast<const uint4*>(xchunk(c * 2 + hc));   // h2, written in P2a
+                    const uint32_t hw[4] = {hq.x, hq.y, hq.z, hq.w};
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const float ha = unpack_lo<FMT>(hw[i]), hb = unpack_hi<FMT>(hw[i]);
+                        dzp[c * 8 + hc * 4 + i] = pack2<FMT>(v[hc * 8 + 2 * i] * fmaf(-ha, ha, 1.0f),
+                                                             v[hc * 8 + 2 * i + 1] * fmaf(-hb, hb, 1.0f));
+                    }
+                }
+            }
+            tc_fence_before();   // Z is read: G2 may overwrite it
+        } else {
+            float dq[KMAX];
+#pragma unroll
+            for (int k = 0; k < KMAX; k++) dq[k] = k < k3 ? xrow[k] : 0.0f;
+#pragma unroll
+            for (int c = 0; c < NCH; c++) {
                 float d[8];
 #pragma unroll
                 for (int i = 0; i < 8; i++) d[i] = 0.0f;
 #pragma unroll
-                for (int k = 0; k < H_MAX_K; k++) {
+                for (int k = 0; k < KMAX; k++) {
                     if (k < k3) {
                         const float4 wa = *reinterpret_cast<const float4*>(W3 + k * HH + c * 8);
                         const float4 wb = *reinterpret_cast<const float4*>(W3 + k * HH + c * 8 + 4);
@@ -462,7 +530,7 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
                         d[6] = fmaf(dq[k], wb.z, d[6]); d[7] = fmaf(dq[k], wb.w, d[7]);
                     }
                 }
-                const uint4 hq = *reinterpret_cast<const uint4*>(Xq + act_chunk_off(wt, c));   // h2, written in P2a
+                const uint4 hq = *reinterpret_cast<const uint4*>(xchunk(c));   // h2, written in P2a
                 const uint32_t hw[4] = {hq.x, hq.y, hq.z, hq.w};
 #pragma unroll
                 for (int i = 0; i < 4; i++) {
@@ -475,9 +543,8 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         mbar_wait(doneW, pw); pw ^= 1u;   // G5 has read X (h2) and NB
         H_TS(10);
 #pragma unroll
-        for (int c = 0; c < 8; c++)
-            *reinterpret_cast<uint4*>(Xq + act_chunk_off(wt, c)) =
-                make_uint4(dzp[c * 4], dzp[c * 4 + 1], dzp[c * 4 + 2], dzp[c * 4 + 3]);
+        for (int c = 0; c < NCH; c++)
+            *reinterpret_cast<uint4*>(xchunk(c)) = make_uint4(dzp[c * 4], dzp[c * 4 + 1], dzp[c * 4 + 2], dzp[c * 4 + 3]);
         fence_async_smem();
         mbar_arrive(ready);
 
@@ -488,7 +555,7 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         tc_fence_after();
         H_TS(12);
 #pragma unroll
-        for (int c = 0; c < 4; c++) {
+        for (int c = 0; c < CPT / 16; c++) {
             float v[16];
             tmem_ld16(zaddr + c * 16, v);
             tmem_ld_wait();
@@ -498,8 +565,8 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
                 const float ha = unpack_lo<FMT>(h1p[c * 8 + i]), hb = unpack_hi<FMT>(h1p[c * 8 + i]);
                 o8[i] = pack2<FMT>(v[2 * i] * fmaf(-ha, ha, 1.0f), v[2 * i + 1] * fmaf(-hb, hb, 1.0f));
             }
-            *reinterpret_cast<uint4*>(Xq + act_chunk_off(wt, c * 2)) = make_uint4(o8[0], o8[1], o8[2], o8[3]);
-            *reinterpret_cast<uint4*>(Xq + act_chunk_off(wt, c * 2 + 1)) = make_uint4(o8[4], o8[5], o8[6], o8[7]);
+            *reinterpret_cast<uint4*>(xchunk(c * 2)) = make_uint4(o8[0], o8[1], o8[2], o8[3]);
+            *reinterpret_cast<uint4*>(xchunk(c * 2 + 1)) = make_uint4(o8[4], o8[5], o8[6], o8[7]);
         }
         tc_fence_before();
         fence_async_smem();
@@ -511,7 +578,7 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
 
     // ---------------- drain: skinny accumulators -> this CTA's slab (x 1/n), diagnostics, output-bias gradients --------
     tc_fence_before();
-    bar_sync(1, H_NCOMP);
+    bar_sync(1, NCOMP);
     tc_fence_after();
     const int P = num_params(O, HH, K);
     float* slab = u.slabs + (size_t)blockIdx.x * slab_stride(P);
@@ -547,27 +614,29 @@ __global__ void __launch_bounds__(H_NTHR, 1) update_h256_kernel(const H256Args a
         red[0 * HR + wt] = (double)rs.pg; red[1 * HR + wt] = (double)rs.v; red[2 * HR + wt] = (double)rs.ent;
         red[3 * HR + wt] = (double)rs.kl; red[4 * HR + wt] = (double)rs.clip;
     }
-    bar_sync(1, H_NCOMP);
-    if (warp < 5) {   // one warp per diagnostic: lane-strided partial sums, then a fixed xor tree (deterministic)
-        double acc = 0.0;
-        for (int m = lane; m < HR; m += 32) acc += red[warp * HR + m];
+    bar_sync(1, NCOMP);
+    // one warp per quantity (5 diagnostics, k3 output-bias gradients, then the unused diagnostic slots): lane-strided
+    // partial sums and a fixed xor tree => deterministic
+    for (int item = warp; item < 5 + k3 + 1; item += 4 * NQ) {
+        if (item < 5) {
+            double acc = 0.0;
+            for (int m = lane; m < HR; m += 32) acc += red[item * HR + m];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (lane == 0) u.dpart[(size_t)blockIdx.x * UPD_NDIAG + warp] = acc;
-    } else if (warp < 5 + H_MAX_K) {
-        const int k = warp - 5;
-        if (k < k3) {
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0) u.dpart[(size_t)blockIdx.x * UPD_NDIAG + item] = acc;
+        } else if (item < 5 + k3) {
+            const int k = item - 5;
             float acc = 0.0f;
             for (int m = lane; m < HR; m += 32) acc += gb[k * HR + m];
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
             if (lane == 0) slab[of.b3 + k] = acc * sc;
+        } else if (lane < UPD_NDIAG - 5) {
+            u.dpart[(size_t)blockIdx.x * UPD_NDIAG + 5 + lane] = 0.0;
         }
-    } else if (warp == 13 && lane < UPD_NDIAG - 5) {
-        u.dpart[(size_t)blockIdx.x * UPD_NDIAG + 5 + lane] = 0.0;
     }
     tc_fence_before();
-    bar_sync(1, H_NCOMP);
+    bar_sync(1, NCOMP);
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
@@ -701,21 +770,27 @@ int h256_reserve(int64_t mb_rows) {
     return PPO_OK;
 }
 
-template <int FMT, int OP>
+template <int FMT, int OP, int KMAX>
 static int launch_h256_t(H256Args& ha, int grid, const CUtensorMap& m128, const CUtensorMap& m64, cudaStream_t st) {
+    constexpr int NQ = 4;   // 16 compute warps of 112 registers; 8 warps of 232 (NQ = 2) measured 4 % slower on B200
     const HLayout L = h_layout(ha.u.d.O, ha.u.d.K);
     const size_t smemA = (size_t)L.end + 1024, smemB = (size_t)DW_STAGES * DW_STAGE_BYTES + 128 + 1024;
     static bool attr_done = false;
     if (!attr_done) {
-        PPO_CUDA(cudaFuncSetAttribute(update_h256_kernel<FMT, OP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        PPO_CUDA(cudaFuncSetAttribute(update_h256_kernel<FMT, OP, NQ, KMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      227 * 1024));
         PPO_CUDA(cudaFuncSetAttribute(dw2_h256_kernel<FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_done = true;
     }
-    update_h256_kernel<FMT, OP><<<grid, H_NTHR, smemA, st>>>(ha, m128);
+    update_h256_kernel<FMT, OP, NQ, KMAX><<<grid, 128 * (NQ + 1), smemA, st>>>(ha, m128);
     PPO_LAUNCH_CHECK();
     dw2_h256_kernel<FMT><<<grid, DW_NTHR, smemB, st>>>(ha, m64);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
+}
+template <int FMT, int OP>
+static int launch_h256_nq(H256Args& ha, int grid, const CUtensorMap& m128, const CUtensorMap& m64, cudaStream_t st) {
+    return ha.u.d.K <= 4 ? launch_h256_t<FMT, OP, 4>(ha, grid, m128, m64, st) : launch_h256_t<FMT, OP, 8>(ha, grid, m128, m64, st);
 }
 
 int launch_update_h256(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st) {
@@ -743,8 +818,8 @@ int launch_update_h256(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st) {
     *grid_out = grid;
     const bool wide = a.d.O + 1 > 4;
     if (fmt == FMT_BF16)
-        return wide ? launch_h256_t<FMT_BF16, 8>(ha, grid, m128, m64, st) : launch_h256_t<FMT_BF16, 4>(ha, grid, m128, m64, st);
-    return wide ? launch_h256_t<FMT_F16, 8>(ha, grid, m128, m64, st) : launch_h256_t<FMT_F16, 4>(ha, grid, m128, m64, st);
+        return wide ? launch_h256_nq<FMT_BF16, 8>(ha, grid, m128, m64, st) : launch_h256_nq<FMT_BF16, 4>(ha, grid, m128, m64, st);
+    return wide ? launch_h256_nq<FMT_F16, 8>(ha, grid, m128, m64, st) : launch_h256_nq<FMT_F16, 4>(ha, grid, m128, m64, st);
 }
 
 }  // namespace ppo

@@ -46,7 +46,7 @@ CheckpointShell* checkpoint_shell_create(int64_t obs, int64_t hidden, int64_t ac
     torch::manual_seed((uint64_t)seed);   // PPO_Discrete.cpp:44
     auto* s = new CheckpointShell();
     s->agent = AgentShell(obs, hidden, actions);
-    s->opt = std::make_unique<torch::optim::AdamW>(s->agent->parameters(), torch::optim::AdamWOptions(lr).eps(1e-5));   // :76-78
+    s->opt = std::make_unique<torch::optim::AdamW>(s->agent->parameters(), torch::optim::AdamWOptions(lr).eps(1e-5f));   // :76-78 (float literal, like the reference)
     return s;
 }
 void checkpoint_shell_destroy(CheckpointShell* s) { delete s; }

@@ -133,6 +133,8 @@ void PPOTrainerBase::loadPolicyFromCheckpoint() {
         if (checkpoint_get_opt_state(m_shell, m.data(), v.data(), &step, &lr)) {
             check(ppo_trainer_set_opt_state(m_b200, m.data(), v.data(), step), "ppo_trainer_set_opt_state");
             m_opt_steps = step;
+            // without annealing the reference never rewrites the optimizer's lr, so a resumed run keeps the archive's
+            if (!m_anneal_lr && lr > 0.0) m_learning_rate = (float)lr;
         }
     }
 }
@@ -144,7 +146,7 @@ void PPOTrainerBase::saveCheckpoint(const std::string& agent_file, const std::st
     check(ppo_trainer_get_params(m_b200, p.data()), "ppo_trainer_get_params");
     check(ppo_trainer_get_opt_state(m_b200, m.data(), v.data(), &step), "ppo_trainer_get_opt_state");
     checkpoint_set_params(m_shell, p.data());
-    checkpoint_set_opt_state(m_shell, m.data(), v.data(), step, m_learning_rate);
+    checkpoint_set_opt_state(m_shell, m.data(), v.data(), step, m_last_lr >= 0.0f ? m_last_lr : m_learning_rate);
     checkpoint_save_agent(m_shell, agent_file);
     checkpoint_save_optimizer(m_shell, optimizer_file);
 }
@@ -157,6 +159,7 @@ ppo_iter_result PPOTrainerBase::iterate(float lr) {
         m_stream = st;
     }
     check(ppo_trainer_iterate(m_b200, lr, &r, m_stream), "ppo_trainer_iterate");
+    m_last_lr = lr;   // what the reference's optimizer holds when it is saved (lr_now, PPO_Discrete.cpp:514-518)
     return r;
 }
 

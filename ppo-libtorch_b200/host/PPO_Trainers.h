@@ -73,6 +73,7 @@ private:
     ppo_trainer* m_b200 = nullptr;
     ppo_host::CheckpointShell* m_shell = nullptr;
     int64_t m_opt_steps = 0;
+    float m_last_lr = -1.0f;                           // learning rate of the last iterate() (what a checkpoint records)
     void* m_stream = nullptr;                          // cudaStream_t the iterations are enqueued on
     template <typename T> void printElement(T t, int width);
 };

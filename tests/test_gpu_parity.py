@@ -438,7 +438,7 @@ def test_permutation_is_bijection(P, batch):
         assert (p.long() == torch.arange(batch, device="cuda")).float().mean().item() < 0.01
 
 
-@pytest.mark.parametrize("batch,n_mb", [(1 << 23, 4), ((1 << 22) + 12345, 4), ((1 << 22) + 7, 3)])
+@pytest.mark.parametrize("batch,n_mb", [(1 << 23, 4), ((1 << 22) + 12346, 4), ((1 << 22) + 7, 3)])
 def test_adv_stats_all_epochs_coalesced_equals_gather(P, request, batch, n_mb):
     """the one-coalesced-pass-per-epoch kernel (inverse permutation, >= 2^22 rows) against the permuted-gather kernel and
     against the materialised permutation: same minibatch membership, sums equal to double rounding"""

@@ -1,0 +1,4 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 300 python tools/h256_timeline.py > gpurun_out/h256_timeline3.txt 2>&1; echo "timeline rc=$?"; grep -E "====|update_minibatch|tile 3" -A14 gpurun_out/h256_timeline3.txt | head -60
+timeout 600 python -m pytest tests/test_gpu_tensorcore.py -x -q -k "h256" > gpurun_out/pytest_h256_nq4.log 2>&1; echo "nq4 rc=$?"; tail -3 gpurun_out/pytest_h256_nq4.log

@@ -22,14 +22,25 @@ def main():
     f = lambda: dev(rng.standard_normal(n).astype(np.float32))   # noqa: E731
     old_lp, adv, ret, old_val = f() * 0.1 - 1.1, f(), f(), f()
     stat = P.ops.adv_stats(adv, n, 1)
-    ts = torch.zeros(64, dtype=torch.int64, device="cuda")
     lib = P.capi.load()
+    run(lib, params, O, H, nvec, obs, acts, old_lp, adv, ret, old_val, n, stat)
+
+
+def run(lib, params, O, H, nvec, obs, acts, old_lp, adv, ret, old_val, n, stat):
+    ts = torch.zeros(64, dtype=torch.int64, device="cuda")
     for it in range(3):
         if it == 2:
             lib.ppo_debug_h256_timeline(P.capi.ptr(ts))
         P.ops.update_minibatch(params, O, H, nvec, obs, acts, old_lp, adv, ret, old_val, 0, n, adv_stat=stat)
     torch.cuda.synchronize()
     lib.ppo_debug_h256_timeline(None)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for it in range(5):
+        P.ops.update_minibatch(params, O, H, nvec, obs, acts, old_lp, adv, ret, old_val, 0, n, adv_stat=stat)
+    ev1.record()
+    torch.cuda.synchronize()
+    print(f"update_minibatch of {n} rows: {ev0.elapsed_time(ev1) / 5:.3f} ms")
     t = ts.cpu().numpy().reshape(4, 16)
     for tile in range(4):
         row = t[tile]
