@@ -38,7 +38,7 @@ extern "C" {
 #define PPO_MAX_LOGITS 64
 
 enum { PPO_OK = 0, PPO_ERR_ARG = 1, PPO_ERR_CUDA = 2, PPO_ERR_UNSUPPORTED = 3, PPO_ERR_COMM = 4 };
-enum { PPO_ENV_CARTPOLE = 0, PPO_ENV_MOUNTAINCAR = 1 };
+enum { PPO_ENV_CARTPOLE = 0, PPO_ENV_MOUNTAINCAR = 1, PPO_ENV_MULTIWALK = 2 };
 /* PPO_ENTROPY_REFERENCE reproduces Distributions/Categorical.cpp:114-117 bit-for-bit in effect
  * (clamp min = FLT_MIN => entropy == -FLT_MIN*sum(p), zero gradient) for UNMASKED heads;
  * masked heads always use the correct formula (CategoricalMasked.cpp:140-142). */
@@ -89,8 +89,14 @@ int ppo_device_count(void);
 int ppo_device_info(int* sm_count, int* cc_major, int* cc_minor);
 /* PPO/Agent.cpp:25-59: parameter count of critic + actor */
 int64_t ppo_num_params(const ppo_dims* dims);
-int ppo_env_state_dim(int kind); /* 4 / 2 */
-int ppo_env_num_actions(int kind); /* 2 / 3 */
+int ppo_env_state_dim(int kind); /* 4 / 2 / 4 */
+int ppo_env_num_actions(int kind); /* 2 / 3 / 3 (logits of the first head) */
+int ppo_env_num_heads(int kind);   /* sub-actions an env consumes per step: 1 / 1 / 8 */
+/* The environment registry (csrc/env.cuh: PPO_ENV_LIST): the reference swaps environments by changing the element type of
+ * m_envs (PPO/PPO_Discrete.h:106, README "Custom Environment Framework"); here an environment is a device functor with a
+ * registered name, and `[b200] env = "<name>"` in PPOConfig.toml picks it.  -1 / NULL for an unknown name / kind. */
+int ppo_env_kind_from_name(const char* name);
+const char* ppo_env_name(int kind);
 
 /* ---- K3: vectorised envs -------------------------------------------------------------- */
 /* Environments/CartPole.cpp:34-45, MountainCar.cpp:60-67 + PPO_Discrete::initEnvs (:365-402).
@@ -101,6 +107,7 @@ int ppo_env_reset(int kind, int n, float* state_soa, int32_t* ep_len, float* ep_
                   ppo_stream_t stream);
 /* CartPole::step (CartPole.cpp:47-94) / MountainCar::step (MountainCar.cpp:29-57) fused with
  * PPO_Discrete::stepEnvs (PPO_Discrete.cpp:413-483): truncation at max_episode_steps (:443),
+ * actions int32 [n, ppo_env_num_heads(kind)] (one sub-action per env for the reference's two environments),
  * auto-reset on done (:453-458), episode statistics.  done_out is 0/1 fp32 as stored in
  * m_dones; fin_len/fin_ret (optional) hold the finished episode's length/return, else 0. */
 int ppo_env_step(int kind, int n, float* state_soa, int32_t* ep_len, float* ep_ret,

@@ -59,6 +59,7 @@ class Oracle:
         L.orc_cartpole_reset.argtypes = [_f32p, _f32p]
         L.orc_mountaincar_reset.argtypes = [_f32p, C.c_float]
         L.orc_mt19937_canonical_f32.argtypes = [C.c_uint32, C.c_int, _f32p]
+        L.orc_multiwalk_mask.argtypes = [_f32p, C.c_void_p]
         L.orc_env_step.argtypes = [C.c_int, C.c_int, _f32p, _i32p, _f32p, _i32p, C.c_int, _f32p,
                                    _f32p, _f32p, _f32p, _i32p, _f32p]
         L.orc_num_params.restype = C.c_int64
@@ -125,6 +126,14 @@ class Oracle:
                             int(max_episode_steps), np.ascontiguousarray(reset_u, np.float32),
                             obs, rew, done, fl, fr)
         return obs, rew, done, fl, fr
+
+    def multiwalk_mask(self, state):
+        """uint8 [n, 21] action mask of MultiWalk states [n, 4]"""
+        state = np.ascontiguousarray(state, np.float32)
+        out = np.zeros((state.shape[0], 21), np.uint8)
+        for i in range(state.shape[0]):
+            self.L.orc_multiwalk_mask(state[i], out[i].ctypes.data_as(C.c_void_p))
+        return out
 
     # -- networks / distributions
     def num_params(self, O, H, K):

@@ -106,15 +106,50 @@ void orc_mountaincar_reset(float* s, float u) {
 
 /* PPO/PPO_Discrete.cpp:429-466: step, truncate at episode_length == max_episode_steps (:443),
  * on done record (len, ret) and reset (:453-458); reward is the step's reward, done -> m_dones. */
+/* ---- MultiWalk: synthetic MultiDiscrete env with a state-dependent mask (no reference counterpart; restates
+ * ppo-libtorch_b200/csrc/env.cuh: MultiWalkEnv operation by operation, -ffp-contract=off keeps the roundings) ---- */
+void orc_multiwalk_reset(float* s, const float* u4) {
+    for (int i = 0; i < 4; i++) s[i] = u4[i] * 1.6f + -0.8f;
+}
+void orc_multiwalk_step(float* s, const int32_t* acts, float* reward, int* terminated) {
+    const float gain = 0.05f * (float)(1 + acts[4]);
+    float dist = 0.0f;
+    for (int i = 0; i < 4; i++) {
+        float p = s[i] + (float)(acts[i] - 1) * gain;
+        p = p < -1.0f ? -1.0f : (p > 1.0f ? 1.0f : p);
+        s[i] = p;
+        dist = dist + fabsf(p);
+    }
+    const float bonus = 0.01f * (float)(acts[5] + acts[6] + acts[7]);
+    *terminated = dist < 0.2f;
+    *reward = *terminated ? 1.0f : bonus - 0.25f * dist;
+}
+/* mask over the 21 logits of nvec {3,3,3,3,3,2,2,2}, one byte per logit */
+void orc_multiwalk_mask(const float* s, uint8_t* mask21) {
+    int small = 1;
+    for (int i = 0; i < 4; i++) {
+        mask21[3 * i + 0] = s[i] > -0.95f;
+        mask21[3 * i + 1] = 1;
+        mask21[3 * i + 2] = s[i] < 0.95f;
+        small = small && fabsf(s[i]) <= 0.7f;
+    }
+    mask21[12] = 1; mask21[13] = 1; mask21[14] = (uint8_t)small;
+    for (int h = 0; h < 3; h++) {
+        mask21[15 + 2 * h] = 1;
+        mask21[16 + 2 * h] = s[h] >= 0.0f;
+    }
+}
+
 void orc_env_step(int kind, int n, float* state, int32_t* ep_len, float* ep_ret,
                   const int32_t* actions, int max_episode_steps, const float* reset_u,
                   float* obs_out, float* reward_out, float* done_out,
                   int32_t* fin_len, float* fin_ret) {
-    const int S = (kind == ORC_ENV_CARTPOLE) ? 4 : 2;
+    const int S = (kind == ORC_ENV_MOUNTAINCAR) ? 2 : 4;
     for (int i = 0; i < n; i++) {
         float* s = state + (size_t)i * S;
         float r; int term;
         if (kind == ORC_ENV_CARTPOLE) orc_cartpole_step(s, actions[i], &r, &term);
+        else if (kind == ORC_ENV_MULTIWALK) orc_multiwalk_step(s, actions + (size_t)i * 8, &r, &term);   /* actions [n, 8] */
         else orc_mountaincar_step(s, actions[i], &r, &term);
         ep_len[i] += 1;              /* CartPole.cpp:90-91 / MountainCar.cpp:51-52 */
         ep_ret[i] += r;
@@ -125,6 +160,7 @@ void orc_env_step(int kind, int n, float* state, int32_t* ep_len, float* ep_ret,
             if (fin_len) fin_len[i] = ep_len[i];
             if (fin_ret) fin_ret[i] = ep_ret[i];
             if (kind == ORC_ENV_CARTPOLE) orc_cartpole_reset(s, reset_u + (size_t)i * 4);
+            else if (kind == ORC_ENV_MULTIWALK) orc_multiwalk_reset(s, reset_u + (size_t)i * 4);
             else orc_mountaincar_reset(s, reset_u[(size_t)i * 4]);
             ep_len[i] = 0;
             ep_ret[i] = 0.0f;

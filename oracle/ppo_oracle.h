@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-enum { ORC_ENV_CARTPOLE = 0, ORC_ENV_MOUNTAINCAR = 1 };
+enum { ORC_ENV_CARTPOLE = 0, ORC_ENV_MOUNTAINCAR = 1, ORC_ENV_MULTIWALK = 2 };
 enum { ORC_ENTROPY_REFERENCE = 0, ORC_ENTROPY_EXACT = 1 };
 
 /* ---- a1..a4: single-env dynamics ------------------------------------------------ */
@@ -38,6 +38,12 @@ void orc_mt19937_canonical_f32(uint32_t seed, int n, float* u_out);
 void orc_mountaincar_step(float* state2, int64_t action, float* reward, int* terminated);
 /* Environments/MountainCar.cpp:60-67,79-88 with injected uniform */
 void orc_mountaincar_reset(float* state2, float u);
+
+/* MultiWalk (synthetic MultiDiscrete env with a state-dependent action mask; csrc/env.cuh: MultiWalkEnv).  No reference
+ * counterpart: parity for this env is against this restatement only ("parity unpinned"). */
+void orc_multiwalk_reset(float* state4, const float* u4);
+void orc_multiwalk_step(float* state4, const int32_t* acts8, float* reward, int* terminated);
+void orc_multiwalk_mask(const float* state4, uint8_t* mask21);
 
 /* ---- a5: vectorised step (PPO/PPO_Discrete.cpp:413-483) ------------------------------ */
 /* state AoS [n,S] (S=4 cartpole, 2 mountaincar); reset_u [n,4] (row i used iff env i resets;

@@ -8,6 +8,6 @@ trainer.py handle on the C++ trainer (PPO_Discrete::train loop body)
 Import name: `ppo_libtorch_b200` (see the shim package of that name at the repo root).
 """
 from . import capi, dp, ops  # noqa: F401
-from .capi import ENTROPY_EXACT, ENTROPY_REFERENCE, ENV_CARTPOLE, ENV_MOUNTAINCAR, PpoError  # noqa: F401
+from .capi import ENTROPY_EXACT, ENTROPY_REFERENCE, ENV_CARTPOLE, ENV_MOUNTAINCAR, ENV_MULTIWALK, PpoError  # noqa: F401
 from .trainer import Trainer, orthogonal_init_params, unique_id  # noqa: F401
 from .classes import Agent, AgentOutput, Categorical, CategoricalMasked  # noqa: F401

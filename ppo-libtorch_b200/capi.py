@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libppo_b200.so")
 
 PPO_MAX_HEADS = 8
-ENV_CARTPOLE, ENV_MOUNTAINCAR = 0, 1
+ENV_CARTPOLE, ENV_MOUNTAINCAR, ENV_MULTIWALK = 0, 1, 2
 ENTROPY_REFERENCE, ENTROPY_EXACT = 0, 1
 MATH_FP32, MATH_BF16, MATH_FP16 = 0, 1, 2
 
@@ -77,6 +77,9 @@ _PROTOS = {
     "ppo_set_math_mode": (C.c_int, [C.c_int]),
     "ppo_get_math_mode": (C.c_int, []),
     "ppo_update_path": (C.c_int, [C.POINTER(Dims)]),
+    "ppo_env_num_heads": (C.c_int, [C.c_int]),
+    "ppo_env_kind_from_name": (C.c_int, [C.c_char_p]),
+    "ppo_env_name": (C.c_char_p, [C.c_int]),
     "ppo_categorical_normalize": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_void_p]),
     "ppo_adv_stats_all_epochs": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint64,

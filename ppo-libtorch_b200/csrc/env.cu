@@ -2,6 +2,8 @@
 // in-kernel truncation + auto-reset + episode statistics).  HBM-bound: 60 B per CartPole
 // env-step, 44 B per MountainCar env-step (+ O*4 B for the observation row).
 // Replaces PPO_Discrete::initEnvs / stepEnvs + ThreadPool (PPO/PPO_Discrete.cpp:365-483).
+#include <string.h>
+
 #include "env.cuh"
 
 namespace ppo {
@@ -43,13 +45,24 @@ __global__ void __launch_bounds__(256) env_step_kernel(
     const int64_t i0 = (int64_t)first + ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * V;
     if (i0 >= n) return;
     float st[S][V];
-    int32_t len[V], act[V];
+    constexpr int AH = Env::HEADS;   // sub-actions per env: actions is int32 [n, AH]
+    int32_t len[V], act[V][AH];
     float ret[V];
 #pragma unroll
     for (int s = 0; s < S; s++) ldv<V>(state + (size_t)s * n + i0, st[s]);
     ldv<V>(ep_len + i0, len);
     ldv<V>(ep_ret + i0, ret);
-    ldv<V>(actions + i0, act);
+    if constexpr (AH == 1) {
+        int32_t a1[V];
+        ldv<V>(actions + i0, a1);
+#pragma unroll
+        for (int v = 0; v < V; v++) act[v][0] = a1[v];
+    } else {
+#pragma unroll
+        for (int v = 0; v < V; v++)
+#pragma unroll
+            for (int h = 0; h < AH; h++) act[v][h] = __ldg(actions + (size_t)(i0 + v) * AH + h);
+    }
     float rew[V], dn[V], fr[V];
     int32_t fl[V];
 #pragma unroll
@@ -60,7 +73,7 @@ __global__ void __launch_bounds__(256) env_step_kernel(
         // Peek whether this transition ends the episode is only known after the step, so the
         // reset draws are produced lazily inside the branch (Philox) or read (parity mode).
         float u[4] = {0.f, 0.f, 0.f, 0.f};
-        StepOut o = Env::step(s_, act[v]);
+        StepOut o = Env::step_multi(s_, act[v]);
         len[v] += 1;
         ret[v] = __fadd_rn(ret[v], o.reward);
         const bool done = o.terminated || (len[v] == max_episode_steps);
@@ -137,7 +150,7 @@ static int launch_step(int n, float* state, int32_t* ep_len, float* ep_ret, cons
     const bool vec_ok = (n % 4 == 0) && al16(state) && al16(ep_len) && al16(ep_ret) && al16(actions) &&
                         al16(reward_out) && al16(done_out) && al16(fin_len) && al16(fin_ret) && al16(obs_out) &&
                         al16(reset_u);
-    if (vec_ok && n >= 4) {
+    if (vec_ok && n >= 4 && Env::HEADS == 1) {
         const int threads = 256, items = n / 4;
         env_step_kernel<Env, 4><<<(items + threads - 1) / threads, threads, 0, st>>>(
             n, 0, state, ep_len, ep_ret, actions, max_episode_steps, reset_u, seed, counter, obs_out, reward_out,
@@ -157,11 +170,29 @@ static int launch_step(int n, float* state, int32_t* ep_len, float* ep_ret, cons
 using namespace ppo;
 
 extern "C" int ppo_env_state_dim(int kind) {
-    return kind == PPO_ENV_CARTPOLE ? CartPoleEnv::S : (kind == PPO_ENV_MOUNTAINCAR ? MountainCarEnv::S : -1);
+    return env_dispatch(kind, [](auto tag) { return (int)decltype(tag)::type::S; }, -1);
 }
 extern "C" int ppo_env_num_actions(int kind) {
-    return kind == PPO_ENV_CARTPOLE ? CartPoleEnv::ACTIONS
-                                    : (kind == PPO_ENV_MOUNTAINCAR ? MountainCarEnv::ACTIONS : -1);
+    return env_dispatch(kind, [](auto tag) { return (int)decltype(tag)::type::ACTIONS; }, -1);
+}
+extern "C" int ppo_env_num_heads(int kind) {
+    return env_dispatch(kind, [](auto tag) { return (int)decltype(tag)::type::HEADS; }, -1);
+}
+// the registry's names: what `[b200] env = "<name>"` in PPOConfig.toml resolves through
+extern "C" int ppo_env_kind_from_name(const char* name) {
+    if (!name) return -1;
+#define PPO_ENV_NAME(id, nm, Env) \
+    if (!strcmp(name, nm)) return id;
+    PPO_ENV_LIST(PPO_ENV_NAME)
+#undef PPO_ENV_NAME
+    return -1;
+}
+extern "C" const char* ppo_env_name(int kind) {
+#define PPO_ENV_NAME(id, nm, Env) \
+    if (kind == id) return nm;
+    PPO_ENV_LIST(PPO_ENV_NAME)
+#undef PPO_ENV_NAME
+    return nullptr;
 }
 
 extern "C" int ppo_env_reset(int kind, int n, float* state_soa, int32_t* ep_len, float* ep_ret,
@@ -170,14 +201,13 @@ extern "C" int ppo_env_reset(int kind, int n, float* state_soa, int32_t* ep_len,
     PPO_REQUIRE(n >= 0 && state_soa && ep_len && ep_ret, "ppo_env_reset: null buffer or negative n");
     if (n == 0) return PPO_OK;
     const int threads = 256, blocks = (n + threads - 1) / threads;
-    if (kind == PPO_ENV_CARTPOLE)
-        env_reset_kernel<CartPoleEnv><<<blocks, threads, 0, as_stream(stream)>>>(n, state_soa, ep_len, ep_ret,
-                                                                                uniforms, seed, counter, obs_out);
-    else if (kind == PPO_ENV_MOUNTAINCAR)
-        env_reset_kernel<MountainCarEnv><<<blocks, threads, 0, as_stream(stream)>>>(n, state_soa, ep_len, ep_ret,
-                                                                                   uniforms, seed, counter, obs_out);
-    else
-        PPO_REQUIRE(false, "ppo_env_reset: unknown env kind %d", kind);
+    const int rc = env_dispatch(kind, [&](auto tag) {
+        using Env = typename decltype(tag)::type;
+        env_reset_kernel<Env><<<blocks, threads, 0, as_stream(stream)>>>(n, state_soa, ep_len, ep_ret, uniforms, seed, counter,
+                                                                        obs_out);
+        return PPO_OK;
+    }, PPO_ERR_ARG);
+    PPO_REQUIRE(rc == PPO_OK, "ppo_env_reset: unknown env kind %d", kind);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
 }
@@ -189,14 +219,12 @@ extern "C" int ppo_env_step(int kind, int n, float* state_soa, int32_t* ep_len, 
     PPO_REQUIRE(n >= 0 && state_soa && ep_len && ep_ret && actions && reward_out && done_out,
                 "ppo_env_step: null buffer or negative n");
     if (n == 0) return PPO_OK;
-    if (kind == PPO_ENV_CARTPOLE)
-        return launch_step<CartPoleEnv>(n, state_soa, ep_len, ep_ret, actions, max_episode_steps, reset_uniforms,
-                                        seed, counter, obs_out, reward_out, done_out, fin_len, fin_ret,
-                                        as_stream(stream));
-    if (kind == PPO_ENV_MOUNTAINCAR)
-        return launch_step<MountainCarEnv>(n, state_soa, ep_len, ep_ret, actions, max_episode_steps,
-                                           reset_uniforms, seed, counter, obs_out, reward_out, done_out, fin_len,
-                                           fin_ret, as_stream(stream));
+    const int rc = env_dispatch(kind, [&](auto tag) {
+        using Env = typename decltype(tag)::type;
+        return launch_step<Env>(n, state_soa, ep_len, ep_ret, actions, max_episode_steps, reset_uniforms, seed, counter,
+                                obs_out, reward_out, done_out, fin_len, fin_ret, as_stream(stream));
+    }, -12345);
+    if (rc != -12345) return rc;
     PPO_REQUIRE(false, "ppo_env_step: unknown env kind %d", kind);
     return PPO_ERR_ARG;
 }

@@ -61,6 +61,8 @@ struct CartPoleEnv {
         return o;
     }
     __device__ static inline uint32_t action_mask(const float (&)[S]) { return 0x3u; }
+    static constexpr int HEADS = 1;   // sub-actions consumed per step
+    __device__ static inline StepOut step_multi(float (&s)[S], const int32_t* acts) { return step(s, acts[0]); }
 };
 
 // Environments/MountainCar.cpp:6-13 (constants), :29-57 (step), :60-67 (reset), :69-77 (mask)
@@ -93,7 +95,91 @@ struct MountainCarEnv {
         return o;
     }
     __device__ static inline uint32_t action_mask(const float (&)[S]) { return 0x7u; }
+    static constexpr int HEADS = 1;
+    __device__ static inline StepOut step_multi(float (&s)[S], const int32_t* acts) { return step(s, acts[0]); }
 };
+
+// MultiWalk: a synthetic MultiDiscrete environment with a STATE-DEPENDENT action mask.  No reference counterpart (the
+// reference's two environments return all-ones masks and its MultiDiscrete trainer feeds a single sub-action to the env,
+// SURVEY.md Q9): it exists to exercise the generic masked multi-head path end to end with the action
+// space the reference keeps commented at PPO/Agent.cpp:16, nvec = {3, 3, 3, 3, 3, 2, 2, 2} (21 logits, 8 heads).
+//   state = four positions in [-1, 1]; heads 0..3 move position i by (a_i - 1) * gain, head 4 picks gain = 0.05 (1 + a_4),
+//   heads 5..7 are binary flags worth 0.01 each; reward = flags - 0.25 * sum |pos|, or +1 when sum |pos| < 0.2 (terminal).
+//   mask: a move that would leave [-0.95, 0.95] is invalid; the largest gain needs every |pos| <= 0.7; flag h may be
+//   raised only while pos[h - 5] >= 0.  Every head always keeps at least one valid option.
+// The CPU restatement is oracle/ppo_oracle.c: orc_multiwalk_* (same operations in the same order).
+struct MultiWalkEnv {
+    static constexpr int S = 4;
+    static constexpr int OBS = 4;
+    static constexpr int ACTIONS = 3;
+    static constexpr int RESET_DRAWS = 4;
+    static constexpr int HEADS = 8;
+
+    __device__ static inline void reset(float (&s)[S], const float (&u)[4]) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) s[i] = __fadd_rn(__fmul_rn(u[i], 1.6f), -0.8f);
+    }
+    __device__ static inline StepOut step_multi(float (&s)[S], const int32_t* acts) {
+        const float gain = __fmul_rn(0.05f, (float)(1 + acts[4]));
+        float dist = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            float p = __fadd_rn(s[i], __fmul_rn((float)(acts[i] - 1), gain));
+            p = p < -1.0f ? -1.0f : (p > 1.0f ? 1.0f : p);
+            s[i] = p;
+            dist = __fadd_rn(dist, fabsf(p));
+        }
+        const float bonus = __fmul_rn(0.01f, (float)(acts[5] + acts[6] + acts[7]));
+        StepOut o;
+        o.terminated = dist < 0.2f;
+        o.reward = o.terminated ? 1.0f : __fsub_rn(bonus, __fmul_rn(0.25f, dist));
+        return o;
+    }
+    __device__ static inline StepOut step(float (&s)[S], int action) {   // single sub-action: the other heads at rest
+        const int32_t acts[8] = {action, 1, 1, 1, 0, 0, 0, 0};
+        return step_multi(s, acts);
+    }
+    __device__ static inline uint32_t action_mask(const float (&s)[S]) {
+        uint32_t m = 0u;
+        bool small = true;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            m |= (s[i] > -0.95f ? 1u : 0u) << (3 * i);
+            m |= 1u << (3 * i + 1);
+            m |= (s[i] < 0.95f ? 1u : 0u) << (3 * i + 2);
+            small = small && fabsf(s[i]) <= 0.7f;
+        }
+        m |= 3u << 12;
+        m |= (small ? 1u : 0u) << 14;
+#pragma unroll
+        for (int h = 0; h < 3; h++) {
+            m |= 1u << (15 + 2 * h);
+            m |= (s[h] >= 0.0f ? 1u : 0u) << (16 + 2 * h);
+        }
+        return m;
+    }
+};
+
+// ---- the environment registry: ONE list.  A new environment = a functor above (S, OBS, ACTIONS, HEADS, RESET_DRAWS,
+// reset, step, step_multi, action_mask) + one X(...) line here + its PPO_ENV_* enumerator in include/ppo_b200.h; every
+// dispatch site (env.cu, rollout.cu, rollout_tc.cu, rollout_h256.cu) and the `[b200] env = "<name>"` key go through it.
+#define PPO_ENV_LIST(X)                                  \
+    X(PPO_ENV_CARTPOLE, "cartpole", CartPoleEnv)         \
+    X(PPO_ENV_MOUNTAINCAR, "mountaincar", MountainCarEnv) \
+    X(PPO_ENV_MULTIWALK, "multiwalk", MultiWalkEnv)
+template <class E>
+struct EnvTag {
+    using type = E;
+};
+// f(EnvTag<Env>{}) for the functor registered under `kind`; `otherwise` when the kind is unknown
+template <class F>
+inline int env_dispatch(int kind, F&& f, int otherwise) {
+#define PPO_ENV_CASE(id, name, Env) \
+    if (kind == id) return f(EnvTag<Env>{});
+    PPO_ENV_LIST(PPO_ENV_CASE)
+#undef PPO_ENV_CASE
+    return otherwise;
+}
 
 // One vectorised transition of env `i` (PPO/PPO_Discrete.cpp:435-466): step, truncate at
 // episode_length == max_episode_steps (:443), on done record (len, ret) and reset (:453-458).

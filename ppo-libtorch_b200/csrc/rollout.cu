@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(MLP_THREADS) rollout_kernel(const RollArgs a) 
                 float u[4] = {0.f, 0.f, 0.f, 0.f};
                 float reward, fr = 0.0f;
                 int32_t fl = 0;
-                StepOut so = Env::step(s, acts[0]);
+                StepOut so = Env::step_multi(s, acts);
                 len += 1;
                 ret = __fadd_rn(ret, so.reward);
                 const bool done = so.terminated || (len == a.cfg.max_episode_steps);
@@ -370,7 +370,7 @@ __global__ void __launch_bounds__(256, 2) rollout64_kernel(const RollArgs a) {
                 if (a.mask_buf)
                     for (int j = 0; j < K; j++) a.mask_buf[row * K + j] = (uint8_t)((mbits >> j) & 1ull);
                 // stepEnvs (:413-483): step, truncate, auto-reset, episode statistics
-                StepOut so = Env::step(s, acts[0]);
+                StepOut so = Env::step_multi(s, acts);
                 len += 1;
                 ret = __fadd_rn(ret, so.reward);
                 const bool done = so.terminated || (len == a.cfg.max_episode_steps);
@@ -455,6 +455,8 @@ static int g_rollout_tc_min = 8192;   // below ~8k envs a step is latency-bound 
 template <class Env>
 static int dispatch_rollout(const RollArgs& a, cudaStream_t st) {
     PPO_REQUIRE(a.d.O == Env::OBS, "rollout: obs_dim=%d but the env observes %d floats", a.d.O, Env::OBS);
+    PPO_REQUIRE(a.d.heads >= Env::HEADS, "rollout: the env consumes %d sub-actions per step but the policy has %d heads",
+                Env::HEADS, a.d.heads);
     // 128-env tensor-core tiles once there are enough envs to fill them (ppo_debug_rollout_impl: 2 = never, 3 = always)
     if (rollout_tc_supported(a.d) && (g_rollout_impl == 3 || (g_rollout_impl == 1 && a.cfg.n_envs >= g_rollout_tc_min)))
         return launch_rollout_tc<Env>(a, st);
@@ -509,9 +511,8 @@ extern "C" int ppo_rollout(const float* params, const ppo_dims* dims, const ppo_
     a.mask_buf = mask_buf; a.ep_stats = ep_stats;
     cudaStream_t st = as_stream(stream);
     int rc;
-    if (cfg->env_kind == PPO_ENV_CARTPOLE) rc = dispatch_rollout<CartPoleEnv>(a, st);
-    else if (cfg->env_kind == PPO_ENV_MOUNTAINCAR) rc = dispatch_rollout<MountainCarEnv>(a, st);
-    else { set_error("ppo_rollout: unknown env kind %d", cfg->env_kind); return PPO_ERR_ARG; }
+    rc = env_dispatch(cfg->env_kind, [&](auto tag) { return dispatch_rollout<typename decltype(tag)::type>(a, st); }, -12345);
+    if (rc == -12345) { set_error("ppo_rollout: unknown env kind %d", cfg->env_kind); return PPO_ERR_ARG; }
     if (rc) return rc;
     if (adv_buf && ret_buf && cfg->n_steps > 0)
         return ppo_gae(cfg->n_steps, cfg->n_envs, rewards_buf, values_buf, dones_buf, next_value, next_done,

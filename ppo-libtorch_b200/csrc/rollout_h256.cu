@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(H_NTHR, 1) rollout_h256_kernel(const RollArgs 
                 if (a.mask_buf)
                     for (int j = 0; j < K; j++) a.mask_buf[row * K + j] = (uint8_t)((mbits >> j) & 1ull);
                 // stepEnvs (:413-483): step, truncate, auto-reset, episode statistics
-                StepOut so = Env::step(s, acts[0]);
+                StepOut so = Env::step_multi(s, acts);
                 len += 1;
                 ret = __fadd_rn(ret, so.reward);
                 const bool fin = so.terminated || (len == a.cfg.max_episode_steps);
@@ -481,5 +481,6 @@ int launch_rollout_h256(const RollArgs& a, int fmt, cudaStream_t st) {
 }
 template int launch_rollout_h256<CartPoleEnv>(const RollArgs&, int, cudaStream_t);
 template int launch_rollout_h256<MountainCarEnv>(const RollArgs&, int, cudaStream_t);
+template int launch_rollout_h256<MultiWalkEnv>(const RollArgs&, int, cudaStream_t);
 
 }  // namespace ppo

@@ -338,7 +338,7 @@ __global__ void __launch_bounds__(RT_NWG * 128, 1) rollout_tc_kernel(const RollA
                 if (a.mask_buf)
                     for (int j = 0; j < K; j++) a.mask_buf[row * K + j] = (uint8_t)((mbits >> j) & 1ull);
                 // stepEnvs (:413-483): step, truncate, auto-reset, episode statistics
-                StepOut so = Env::step(s, acts[0]);
+                StepOut so = Env::step_multi(s, acts);
                 len += 1;
                 ret = __fadd_rn(ret, so.reward);
                 const bool fin = so.terminated || (len == a.cfg.max_episode_steps);
@@ -407,5 +407,6 @@ int launch_rollout_tc(const RollArgs& a, cudaStream_t st) {
 }
 template int launch_rollout_tc<CartPoleEnv>(const RollArgs&, cudaStream_t);
 template int launch_rollout_tc<MountainCarEnv>(const RollArgs&, cudaStream_t);
+template int launch_rollout_tc<MultiWalkEnv>(const RollArgs&, cudaStream_t);
 
 }  // namespace ppo

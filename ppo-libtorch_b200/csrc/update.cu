@@ -331,8 +331,13 @@ __device__ __forceinline__ float ld_sys_f32(const float* p) {
 __device__ __forceinline__ void st_sys_u32(unsigned* p, unsigned v) {
     asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ void st_sys_f32(float* p, float v) {
-    asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+__device__ __forceinline__ void st_sys_u64(uint64_t* p, uint64_t v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_sys_u64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
 }
 __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel(
     const float* __restrict__ slabs, const double* __restrict__ dpart, int nslabs, int P, int64_t stride, float inv_n,
@@ -349,7 +354,6 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel
     const int64_t px = peer_px(P);
     const int W = pa.world;
     const int64_t slot_off = (int64_t)(seq & 1u) * peer_slot_bytes(P, W);
-    const int64_t flags_off = slot_off + (int64_t)W * px * 4;    // flags[world][PEER_NB] behind data[world][px]
     if (threadIdx.x == 0) s_fail = 0u;
     pdl_trigger();
     pdl_wait();
@@ -367,15 +371,20 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel
     }
     part[pt][col] = acc;
     __syncthreads();
-    // ---- push this rank's column block (and, from block 0, its 8 diagnostics) into EVERY rank's buffer, row [rank]
+    // ---- push this rank's column block (and, from block 0, its 8 diagnostics) into EVERY rank's buffer, row [rank].
+    // Every value travels as ONE 8-byte word {step number, fp32 bits} (the "LL" protocol): an aligned 8-byte store is
+    // single-copy atomic, so the receiver polls the word itself until its tag is this step's - no flag array, no
+    // system-scope fence between data and flag (a fence behind remote stores waits for their acknowledgement, i.e. a
+    // full NVLink round trip: the first push version with separate flags cost the same ~11 us per step as the pull one).
+    const uint64_t tag = (uint64_t)seq << 32;
     if (pt == 0 && i < P) {
         double t = part[0][col];
 #pragma unroll
         for (int q = 1; q < RED_PARTS; q++) t += part[q][col];
-        const float g = (float)t;
+        const uint64_t word = tag | (uint64_t)__float_as_uint((float)t);
 #pragma unroll
         for (int r = 0; r < PEER_MAX; r++)
-            if (r < W) st_sys_f32(reinterpret_cast<float*>(pa.xchg[r] + slot_off) + (int64_t)pa.rank * px + i, g);
+            if (r < W) st_sys_u64(reinterpret_cast<uint64_t*>(pa.xchg[r] + slot_off) + (int64_t)pa.rank * px + i, word);
     }
     if (blockIdx.x == 0 && threadIdx.x >= 64 && threadIdx.x < 96) {
         const int l = threadIdx.x - 64;
@@ -394,47 +403,46 @@ __global__ void __launch_bounds__(RED_COLS * RED_PARTS) reduce_peer_apply_kernel
 #pragma unroll
             for (int q = 0; q < 8; q++)
                 if (q == l) dv = d8[q];
+            const uint64_t word = tag | (uint64_t)__float_as_uint(dv);
 #pragma unroll
             for (int r = 0; r < PEER_MAX; r++)
-                if (r < W) st_sys_f32(reinterpret_cast<float*>(pa.xchg[r] + slot_off) + (int64_t)pa.rank * px + px - 64 + l, dv);
+                if (r < W)
+                    st_sys_u64(reinterpret_cast<uint64_t*>(pa.xchg[r] + slot_off) + (int64_t)pa.rank * px + px - 64 + l, word);
         }
     }
-    // release: the CTA barrier orders every thread's data stores before the flag writers' system-scope fences (fences
-    // are cumulative); thread r then raises flags[rank][block] in rank r's buffer
-    __syncthreads();
-    if (threadIdx.x < W) {
-        __threadfence_system();
-        st_sys_u32(reinterpret_cast<unsigned*>(pa.xchg[threadIdx.x] + flags_off) + pa.rank * PEER_NB + blockIdx.x, seq);
-    }
-    // ---- wait, in LOCAL memory, for the same block of every rank (bounded spin: a missing peer sets *err, no GPU hang)
-    if (threadIdx.x < W) {
-        const unsigned* pf = reinterpret_cast<const unsigned*>(pa.xchg[pa.rank] + flags_off) + threadIdx.x * PEER_NB + blockIdx.x;
+    // ---- receive, in LOCAL memory: every thread polls the world's words of its own column (bounded spin: a missing peer
+    // sets *err and the step is skipped, no GPU hang), then sums them in rank order
+    const uint64_t* mine = reinterpret_cast<const uint64_t*>(pa.xchg[pa.rank] + slot_off);
+    const long long spin_lim = pa.spin_cycles > 0 ? pa.spin_cycles : 40000000000ll;
+    auto receive = [&](int64_t idx) -> float {
+        uint64_t w[PEER_MAX];
         const long long t0 = clock64();
-        const long long lim = pa.spin_cycles > 0 ? pa.spin_cycles : 40000000000ll;
-        while ((int)(ld_sys_u32(pf) - seq) < 0) {
-            if (clock64() - t0 > lim) { atomicExch(pa.err, 1u); s_fail = 1u; break; }
-        }
-        __threadfence_system();   // acquire side: only the polling threads, then the barrier hands it to the CTA
-    }
-    __syncthreads();
-    // ---- totals in rank order
-    const float* mine = reinterpret_cast<const float*>(pa.xchg[pa.rank] + slot_off);
-    double sq = 0.0;
-    if (pt == 0 && i < P) {
-        float v[PEER_MAX];
+        for (;;) {
+            bool all = true;
 #pragma unroll
-        for (int r = 0; r < PEER_MAX; r++) v[r] = r < W ? ld_sys_f32(mine + (int64_t)r * px + i) : 0.0f;   // loads in flight together
+            for (int r = 0; r < PEER_MAX; r++) {
+                w[r] = r < W ? ld_sys_u64(mine + (int64_t)r * px + idx) : tag;   // the world's loads in flight together
+            }
+#pragma unroll
+            for (int r = 0; r < PEER_MAX; r++) all = all && (uint32_t)(w[r] >> 32) == seq;
+            if (all) break;
+            if (clock64() - t0 > spin_lim) { atomicExch(pa.err, 1u); s_fail = 1u; break; }
+        }
         float g = 0.0f;
 #pragma unroll
         for (int r = 0; r < PEER_MAX; r++)
-            if (r < W) g += v[r];
+            if (r < W) g += __uint_as_float((uint32_t)w[r]);
+        return g;
+    };
+    double sq = 0.0;
+    if (pt == 0 && i < P) {
+        const float g = receive(i);
         grads_out[i] = g;
         sq = (double)g * (double)g;
     }
     if (blockIdx.x == 0 && threadIdx.x >= 64 && threadIdx.x < 72) {
         const int l = threadIdx.x - 64;
-        float dv = 0.0f;
-        for (int r = 0; r < W; r++) dv += ld_sys_f32(mine + (int64_t)r * px + px - 64 + l);
+        const float dv = receive(px - 64 + l);
         if (diag_out) diag_out[l] = dv;
         if (f.diag_hist) f.diag_hist[l] = dv;
     }

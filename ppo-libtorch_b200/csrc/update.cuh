@@ -68,18 +68,15 @@ struct UpdArgs {
 
 // Data-parallel variant of the fused tail: the allreduce happens INSIDE the reduction kernel over peer memory (NVLink
 // P2P stores into the other ranks' exchange buffers, mapped with CUDA IPC), so gradient exchange + clip + AdamW is one
-// launch per rank instead of reduce_kernel -> ncclAllReduce -> clip_adamw_kernel.  PUSH model: exchange buffer of a rank
-// (one cudaMalloc) = two slots (optimiser step parity), each {data[world][peer_px(P)] floats, flags[world][PEER_NB] uint32}.
-// CTA b of rank r STORES its 64 reduced columns into data[r] of EVERY rank's buffer (its own included), fences at system
-// scope and stores the step number into flags[r][b] of every rank; it then polls only its OWN buffer's flags[*][b] (local
-// memory) and sums the world's column blocks in rank order (=> bit-identical totals on every rank).  One one-way NVLink
-// latency per optimiser step; the pull model this replaces paid two dependent round trips (remote flag poll, then remote
-// column loads).  Slot reuse two steps later is safe: a peer publishes step s+1 only after its step-s reads.
+// launch per rank instead of reduce_kernel -> ncclAllReduce -> clip_adamw_kernel.  PUSH model, LL words: exchange buffer of
+// a rank (one cudaMalloc) = two slots (optimiser step parity) of uint64 [world][peer_px(P)].  CTA b of rank r STORES its 64
+// reduced columns as {step number, fp32 bits} words into row r of EVERY rank's buffer (its own included) and then polls the
+// words of its columns in its OWN buffer until every row carries this step's tag, summing them in rank order (=>
+// bit-identical totals on every rank).  One one-way NVLink latency per optimiser step, no flags, no system fence.
+// Slot reuse two steps later is safe: a peer publishes step s+1 only after its step-s reads.
 constexpr int PEER_MAX = 8, PEER_NB = 256;
 __host__ __device__ inline int64_t peer_px(int P) { return (((int64_t)P + 63) & ~(int64_t)63) + 64; }   // + diagnostics
-__host__ __device__ inline int64_t peer_slot_bytes(int P, int world) {
-    return (int64_t)world * (peer_px(P) * 4 + PEER_NB * 4);
-}
+__host__ __device__ inline int64_t peer_slot_bytes(int P, int world) { return (int64_t)world * peer_px(P) * 8; }
 struct PeerArgs {
     int world, rank;
     char* xchg[PEER_MAX];   // every rank's exchange buffer as mapped in THIS process (xchg[rank] = the local one)

@@ -41,10 +41,14 @@ void PPOTrainerBase::build() {
     if (!m_use_cuda) throw std::runtime_error("use_cuda = false: the B200 path has no CPU fallback (run the reference's CPU path)");
     if (ppo_device_count() <= 0) throw std::runtime_error("no CUDA device visible: the B200 path has no CPU fallback");
     std::string env = m_config.env.empty() ? (m_multidiscrete ? "mountaincar" : "cartpole") : m_config.env;
-    int kind;
-    if (env == "cartpole") kind = PPO_ENV_CARTPOLE;
-    else if (env == "mountaincar") kind = PPO_ENV_MOUNTAINCAR;
-    else throw std::runtime_error("[b200] env = \"" + env + "\": expected \"cartpole\" or \"mountaincar\"");
+    // the environment registry (csrc/env.cuh: PPO_ENV_LIST) resolves the name; the reference fixes the env by the element
+    // type of m_envs (PPO/PPO_Discrete.h:106)
+    const int kind = ppo_env_kind_from_name(env.c_str());
+    if (kind < 0) {
+        std::string known;
+        for (int k = 0; ppo_env_name(k); k++) known += std::string(k ? ", " : "") + "\"" + ppo_env_name(k) + "\"";
+        throw std::runtime_error("[b200] env = \"" + env + "\": not a registered environment (" + known + ")");
+    }
     if (ppo_env_state_dim(kind) != m_obs_size)   // initEnvs' size check (PPO_Discrete.cpp:370-375)
         throw std::runtime_error("obs_size " + std::to_string(m_obs_size) + " does not match the environment's observation (" +
                                  std::to_string(ppo_env_state_dim(kind)) + " floats)");
@@ -52,6 +56,9 @@ void PPOTrainerBase::build() {
     // MultiDiscrete nvec the reference keeps commented at Agent.cpp:16 through `[b200] nvec = [..]`
     std::vector<int64_t> nvec = {m_action_size};
     if (m_multidiscrete && !m_config.nvec.empty()) nvec = m_config.nvec;
+    if ((int)nvec.size() < ppo_env_num_heads(kind))
+        throw std::runtime_error("environment \"" + env + "\" consumes " + std::to_string(ppo_env_num_heads(kind)) +
+                                 " sub-actions per step: give PPO_MultiDiscrete its action space with [b200] nvec = [..]");
     if (nvec.size() > PPO_MAX_HEADS) throw std::runtime_error("[b200] nvec: at most " + std::to_string(PPO_MAX_HEADS) + " heads");
     int64_t sumK = 0;
     for (int64_t k : nvec) {

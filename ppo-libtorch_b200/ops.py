@@ -11,7 +11,7 @@ import torch
 from . import capi
 from .capi import Dims, Hyper, RolloutCfg, check, load, ptr, stream_ptr
 
-_S = {capi.ENV_CARTPOLE: 4, capi.ENV_MOUNTAINCAR: 2}
+_S = {capi.ENV_CARTPOLE: 4, capi.ENV_MOUNTAINCAR: 2, capi.ENV_MULTIWALK: 4}
 
 
 def _cuda_required():

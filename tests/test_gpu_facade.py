@@ -194,3 +194,44 @@ def test_reference_driver_source_runs_on_the_facade(tmp_path):
     out = run(REF_DRIVER, str(tmp_path), 3 * BATCH, True)
     assert out.count("|    total_timesteps      | ") == 2 and "Error Occured" not in out
     assert (tmp_path / "Models" / f"PPO_Agent_{3 * BATCH}_steps.pt").exists()
+
+
+MULTIWALK_TOML = """[environment]
+obs_size = 4
+action_size = 21
+max_episode_steps = 50
+[general]
+seed = 2
+total_timesteps = {total}
+use_cuda = true
+checkpoint_updates = 100
+[ppo]
+learning_rate = 1e-3
+num_envs = 256
+num_steps = 16
+num_minibatches = 4
+update_epochs = 2
+ent_coef = 0.01
+[b200]
+env = "multiwalk"
+nvec = [3, 3, 3, 3, 3, 2, 2, 2]
+"""
+
+
+def test_multidiscrete_facade_runs_the_masked_multihead_env(exe, tmp_path):
+    """PPO_MultiDiscrete with `[b200] env = "multiwalk"` and the MultiDiscrete action space the reference keeps commented at
+    PPO/Agent.cpp:16: eight CategoricalMasked heads, masks from the env functor every step."""
+    with open(tmp_path / "PPOConfig.toml", "w") as f:
+        f.write(MULTIWALK_TOML.format(total=4 * 256 * 16))
+    p = subprocess.run([exe, "multidiscrete"], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert p.stdout.count("|    total_timesteps      | ") == 3
+    m = re.search(r"\|    entropy_loss         \| (-?[0-9.]+)", p.stdout)
+    assert m and float(m.group(1)) < -1.0            # -(sum of eight heads' entropies)
+    sd = torch.jit.load(str(tmp_path / "Models" / f"PPO_Agent_{4 * 256 * 16}_steps.pt")).state_dict()
+    assert tuple(sd["m_Actor.actorOutputLayer.weight"].shape) == (21, 64)
+    # an unregistered name is refused with the registry's names in the message
+    with open(tmp_path / "PPOConfig.toml", "w") as f:
+        f.write(MULTIWALK_TOML.format(total=4096).replace('"multiwalk"', '"pong"'))
+    p = subprocess.run([exe, "multidiscrete"], cwd=tmp_path, capture_output=True, text=True, timeout=120)
+    assert p.returncode == 1 and "not a registered environment" in p.stdout and "multiwalk" in p.stdout

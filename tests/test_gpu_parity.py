@@ -760,3 +760,108 @@ def test_trainer_in_kernel_tail_equals_reduce_apply_launch(P, request):
     assert np.array_equal(out[0][1][0], out[1][1][0]) and np.array_equal(out[0][1][1], out[1][1][1])
     for key in ("loss", "grad_norm", "approx_kl"):
         assert out[0][2][key] == out[1][2][key], key
+
+
+# ------------------------------------------------------------------------------- masked multi-head path end to end (f3)
+MW_NVEC = [3, 3, 3, 3, 3, 2, 2, 2]
+
+
+def test_env_registry_names(P):
+    lib = P.capi.load()
+    assert [lib.ppo_env_name(k) for k in range(3)] == [b"cartpole", b"mountaincar", b"multiwalk"] and lib.ppo_env_name(3) is None
+    assert lib.ppo_env_kind_from_name(b"multiwalk") == P.capi.ENV_MULTIWALK and lib.ppo_env_kind_from_name(b"pong") == -1
+    assert [lib.ppo_env_num_heads(k) for k in range(3)] == [1, 1, 8]
+
+
+@pytest.mark.parametrize("H,n,T", [(64, 300, 12), (128, 70, 6)])
+def test_fused_rollout_multiwalk_masked_multihead_vs_oracle(P, orc, H, n, T):
+    """MultiWalk (csrc/env.cuh; oracle/ppo_oracle.c restates it): 8 heads over 21 logits with a mask that DEPENDS ON THE
+    STATE, produced by the env functor inside the fused rollout kernel every step.  Per step, from the GPU's own
+    observation: mask = oracle mask of that state, actions = oracle's masked inverse-CDF sample on the same Philox
+    uniforms (outside the 2^-20 CDF band), log-prob summed over heads, env transition with all 8 sub-actions."""
+    from philox_np import reset_uniforms, sample_uniforms
+    kind, O, nvec = P.capi.ENV_MULTIWALK, 4, MW_NVEC
+    K, heads = sum(nvec), len(nvec)
+    seed, counter, base, max_ep = 777, 40, 16, 7
+    params = P.orthogonal_init_params(O, H, nvec, seed=11)
+    params[-K:] = np.linspace(-0.5, 0.5, K)
+    u0 = np.random.default_rng(1).uniform(size=(n, 4)).astype(np.float32)
+    state, ep_len, ep_ret, _ = P.ops.env_reset(kind, n, uniforms=dev(u0))
+    next_done = torch.zeros(n, device="cuda")
+    out = P.ops.rollout(dev(params), O, H, nvec, kind, state, ep_len, ep_ret, next_done, T, max_ep, 0.98, 0.95,
+                        masked=True, seed=seed, counter=counter, env_id_base=base)
+    o = {k: (v.cpu().numpy() if v is not None else None) for k, v in out.items()}
+    o_len, o_ret = np.zeros(n, np.int32), np.zeros(n, np.float32)
+    prev_done = np.zeros(n, np.float32)
+    ids = np.arange(n) + base
+    seen_invalid = 0
+    for t in range(T):
+        obs_t = o["obs"][t]
+        assert np.array_equal(o["dones"][t], prev_done)
+        mask = orc.multiwalk_mask(obs_t)
+        assert np.array_equal(o["masks"][t], mask)                      # the env functor's mask, stored per step
+        seen_invalid += int((mask == 0).sum())
+        logits, val = orc.mlp_forward(params, O, H, K, obs_t)
+        close(o["values"][t], val, rtol=1e-5, atol=2e-6)
+        u = sample_uniforms(seed, ids, counter + t, heads)
+        oa, _, _, pr, _ = orc.categorical(logits, nvec, mask=mask, uniforms=u, want_probs=True)
+        ga = o["actions"][t]
+        off, edge = 0, np.zeros((n, heads), bool)
+        for h, k in enumerate(nvec):
+            cdf = np.cumsum(pr[:, off:off + k].astype(np.float64), 1)
+            edge[:, h] = np.min(np.abs(cdf - u[:, h:h + 1]), 1) < 2.0 ** -20
+            off += k
+        assert np.all((ga == oa) | edge)
+        assert np.all(mask[np.arange(n)[:, None], np.cumsum([0] + nvec[:-1])[None, :] + ga] == 1)   # never a masked action
+        _, olp2, oent = orc.categorical(logits, nvec, mask=mask, actions=ga)
+        close(o["logprobs"][t], olp2, rtol=1e-5, atol=4e-6)
+        ru = reset_uniforms(seed, ids, counter + t)
+        st = obs_t.copy()
+        oobs, orew, odone, ofl, ofr = orc.env_step(kind, st, o_len, o_ret, ga.astype(np.int32), max_ep, ru)
+        assert np.array_equal(o["rewards"][t], orew)
+        assert np.array_equal(o["fin_len"][t], np.asarray(ofl).astype(np.int32))
+        nxt = o["obs"][t + 1] if t + 1 < T else state.cpu().numpy().T
+        close(nxt, oobs, rtol=1e-6, atol=1e-7)
+        prev_done = odone
+    assert seen_invalid > 0, "the mask never excluded anything: the test would not exercise masking"
+    assert np.array_equal(next_done.cpu().numpy(), prev_done)
+    oadv, oret = orc.gae(o["rewards"], o["values"], o["dones"], o["next_value"], prev_done, 0.98, 0.95)
+    assert np.array_equal(o["adv"], oadv) and np.array_equal(o["ret"], oret)
+
+
+def test_trainer_multiwalk_iteration_matches_composed_oracle(P, orc):
+    """One trainer iteration on MultiWalk (8 masked heads, nvec {3,3,3,3,3,2,2,2}) replayed with the oracle from the
+    trainer's own rollout buffers, masks included: minibatch gradients (fp32 kernels, 1e-4) and the optimiser steps."""
+    N, T, MB, E = 64, 16, 2, 2
+    tr = P.Trainer(env_kind=P.capi.ENV_MULTIWALK, obs_dim=4, nvec=tuple(MW_NVEC), num_envs=N, num_steps=T,
+                   num_minibatches=MB, update_epochs=E, max_episode_steps=20, masked=True, ent_coef=0.01,
+                   entropy_mode=P.capi.ENTROPY_EXACT, seed=5)
+    K, heads = sum(MW_NVEC), len(MW_NVEC)
+    params = tr.get_params().copy()
+    lr = 1e-3
+    tr.rollout(lr)
+    torch.cuda.synchronize()
+    B, mb = N * T, N * T // MB
+    b = {k: tr.buffer(k).cpu().numpy().copy() for k in ("obs", "actions", "logprobs", "adv", "ret", "values", "masks")}
+    obs, acts, masks = b["obs"].reshape(B, 4), b["actions"].reshape(B, heads), b["masks"].reshape(B, K)
+    assert np.array_equal(masks, orc.multiwalk_mask(obs)) and (masks == 0).any()
+    m, v, step = np.zeros_like(params), np.zeros_like(params), 0
+    for e in range(E):
+        tr.begin_epoch(e)
+        torch.cuda.synchronize()
+        perm = tr.buffer("perm").cpu().numpy().copy()
+        for k in range(MB):
+            tr.minibatch_grads(k)
+            torch.cuda.synchronize()
+            g = tr.buffer("grads").cpu().numpy()[:params.size].copy()
+            tr.apply()
+            rows = perm[k * mb:(k + 1) * mb]
+            og, _ = orc.minibatch_grads(params, 4, 64, np.array(MW_NVEC, np.int32), obs[rows], acts[rows], b["logprobs"][rows],
+                                        b["adv"][rows], b["ret"][rows], b["values"][rows], mask=masks[rows], ent_coef=0.01,
+                                        entropy_mode=P.capi.ENTROPY_EXACT)
+            np.testing.assert_allclose(g, og, rtol=1e-4, atol=3e-6 * np.abs(og).max())
+            step += 1
+            orc.clip_adamw(params, og, m, v, lr, step)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(tr.get_params(), params, rtol=2e-5, atol=2e-7)
+    tr.close()

@@ -325,6 +325,25 @@ def test_trainer_h256_mountaincar_default_mode(P):
     assert np.array_equal(outs[0][0], outs[1][0]), "graph replay and eager launches must give identical parameters"
 
 
+def test_trainer_multiwalk_default_mode(P):
+    """the masked 8-head MultiDiscrete path (MultiWalk, nvec {3,3,3,3,3,2,2,2}: 21 logits) through the trainer in the default
+    16-bit mode: the tcgen05 update kernel serves 21 logits with one compute warpgroup per CTA; graph replay = eager."""
+    nvec = (3, 3, 3, 3, 3, 2, 2, 2)
+    assert P.ops.update_path(4, 64, list(nvec)) == 1
+    kw = dict(env_kind=P.capi.ENV_MULTIWALK, obs_dim=4, hidden=64, nvec=nvec, num_envs=1024, num_steps=16, num_minibatches=4,
+              update_epochs=3, max_episode_steps=50, masked=True, ent_coef=0.01, entropy_mode=P.capi.ENTROPY_EXACT, seed=3)
+    outs = []
+    for graph in (False, True):
+        tr = P.Trainer(use_cuda_graph=graph, **kw)
+        rs = [tr.iterate(1e-3) for _ in range(4)]
+        outs.append((tr.get_params(), rs))
+        tr.close()
+    for p, rs in outs:
+        assert np.isfinite(p).all() and all(np.isfinite(r["loss"]) and r["grad_norm"] > 0 for r in rs)
+        assert rs[0]["entropy"] > 1.0          # eight heads: the summed entropy of a near-uniform masked policy
+    assert np.array_equal(outs[0][0], outs[1][0])
+
+
 # ------------------------------------------------------------------------------- the trainer in its default mode
 def _run_trainer(P, mode, iters, **kw):
     prev = P.ops.get_math_mode()
