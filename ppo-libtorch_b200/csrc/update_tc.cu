@@ -918,21 +918,23 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
         gbc[tid] = gb3c;
     }
     bar_sync(3, NWG * 128);
-    // one warp per quantity: lane-strided partial sums, then a fixed xor tree (deterministic)
-    if (warp < 5) {
-        double acc = 0.0;
-        for (int m = lane; m < NT; m += 32) acc += red[warp * NT + m];
+    // one warp per quantity (5 diagnostics, the critic's output-bias gradient, K actor output-bias gradients), dealt round
+    // robin over the NWG * 4 compute warps: lane-strided partial sums, then a fixed xor tree (deterministic)
+    for (int item = warp; item < 6 + K; item += NWG * 4) {
+        if (item < 5) {
+            double acc = 0.0;
+            for (int m = lane; m < NT; m += 32) acc += red[item * NT + m];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (lane == 0) a.dpart[(size_t)blockIdx.x * UPD_NDIAG + warp] = acc;
-    } else if (warp == 5) {
-        float acc = 0.0f;
-        for (int m = lane; m < NT; m += 32) acc += gbc[m];
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0) a.dpart[(size_t)blockIdx.x * UPD_NDIAG + item] = acc;
+        } else if (item == 5) {
+            float acc = 0.0f;
+            for (int m = lane; m < NT; m += 32) acc += gbc[m];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (lane == 0) slab[offs[1].b3] = acc * sc;
-    } else {
-        for (int q = warp - 6; q < K; q += NWG * 4 - 6) {
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0) slab[offs[1].b3] = acc * sc;
+        } else {
+            const int q = item - 6;
             float acc = 0.0f;
             for (int g = 0; g < NWG; g++) {
                 const float* b = reinterpret_cast<const float*>(sm + L.wg0 + g * L.wg_stride + L.b3);

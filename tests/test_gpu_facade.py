@@ -227,7 +227,7 @@ def test_multidiscrete_facade_runs_the_masked_multihead_env(exe, tmp_path):
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
     assert p.stdout.count("|    total_timesteps      | ") == 3
     m = re.search(r"\|    entropy_loss         \| (-?[0-9.]+)", p.stdout)
-    assert m and float(m.group(1)) < -1.0            # -(sum of eight heads' entropies)
+    assert m and float(m.group(1)) > 1.0             # the summed entropy of eight near-uniform heads
     sd = torch.jit.load(str(tmp_path / "Models" / f"PPO_Agent_{4 * 256 * 16}_steps.pt")).state_dict()
     assert tuple(sd["m_Actor.actorOutputLayer.weight"].shape) == (21, 64)
     # an unregistered name is refused with the registry's names in the message

@@ -221,6 +221,9 @@ def test_update_tc_config_e_shard_rows(P, orc, math_mode):
     tensor memory and the fp16 operand tiles are per-row quantities, so nothing leaves fp16 range."""
     O, nvec, H, n = 4, [2], 64, 4194304
     c = _make_case(P, orc, O, nvec, n, False, seed=77, H=H)
+    # advantages correlated with the action: without it the expected policy gradient is ~0 and at 4 M rows the
+    # comparison would measure the noise floor (|g| ~ 1 / sqrt(n)) instead of the kernel
+    c["adv"] = (c["adv"] + 2.0 * (c["acts"][:, 0] == 0)).astype(np.float32)
     rows = c["perm"]
     hyp = dict(clip_coef=0.2, clip_vloss=True)
     dperm = dev(c["perm"])
