@@ -12,6 +12,7 @@
 // With use_cuda_graph the whole iteration is captured once and replayed; the values that change
 // between iterations (learning rate, optimiser step, RNG counters) live in device scalars.
 #include <cstddef>
+#include <stdlib.h>
 #include <string.h>
 
 #include <map>

@@ -179,5 +179,22 @@ __device__ __forceinline__ float unpack_hi(uint32_t v) {
     else { float f; asm("{.reg .b16 l, h; mov.b32 {l, h}, %1; cvt.f32.f16 %0, h;}" : "=f"(f) : "r"(v)); return f; }
 }
 
+// tanh derivative on packed 16-bit pairs: d * (1 - h^2) for two elements in three instructions (pack d, fused
+// -h*h+1, multiply) instead of unpacking h, two fp32 FMAs, two multiplies and the pack.  Each result carries the same
+// single 16-bit rounding it gets when it is stored as a GEMM operand anyway.
+template <int FMT>
+__device__ __forceinline__ uint32_t dtanh2(float d_lo, float d_hi, uint32_t h) {
+    const uint32_t d = pack2<FMT>(d_lo, d_hi), nh = h ^ 0x80008000u;
+    uint32_t g, r;
+    if constexpr (FMT == FMT_BF16) {
+        asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(g) : "r"(nh), "r"(h), "r"(0x3F803F80u));
+        asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(d), "r"(g));
+    } else {
+        asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(g) : "r"(nh), "r"(h), "r"(0x3C003C00u));
+        asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(d), "r"(g));
+    }
+    return r;
+}
+
 }  // namespace umma
 }  // namespace ppo

@@ -502,11 +502,8 @@ __global__ void __launch_bounds__(128 * (NQ + 1), 1)
                     const uint4 hq = *reinterpret_cast<const uint4*>(xchunk(c * 2 + hc));   // h2, written in P2a
                     const uint32_t hw[4] = {hq.x, hq.y, hq.z, hq.w};
 #pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const float ha = unpack_lo<FMT>(hw[i]), hb = unpack_hi<FMT>(hw[i]);
-                        dzp[c * 8 + hc * 4 + i] = pack2<FMT>(v[hc * 8 + 2 * i] * fmaf(-ha, ha, 1.0f),
-                                                             v[hc * 8 + 2 * i + 1] * fmaf(-hb, hb, 1.0f));
-                    }
+                    for (int i = 0; i < 4; i++)
+                        dzp[c * 8 + hc * 4 + i] = dtanh2<FMT>(v[hc * 8 + 2 * i], v[hc * 8 + 2 * i + 1], hw[i]);
                 }
             }
             tc_fence_before();   // Z is read: G2 may overwrite it
@@ -533,10 +530,7 @@ __global__ void __launch_bounds__(128 * (NQ + 1), 1)
                 const uint4 hq = *reinterpret_cast<const uint4*>(xchunk(c));   // h2, written in P2a
                 const uint32_t hw[4] = {hq.x, hq.y, hq.z, hq.w};
 #pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const float ha = unpack_lo<FMT>(hw[i]), hb = unpack_hi<FMT>(hw[i]);
-                    dzp[c * 4 + i] = pack2<FMT>(d[2 * i] * fmaf(-ha, ha, 1.0f), d[2 * i + 1] * fmaf(-hb, hb, 1.0f));
-                }
+                for (int i = 0; i < 4; i++) dzp[c * 4 + i] = dtanh2<FMT>(d[2 * i], d[2 * i + 1], hw[i]);
             }
         }
         H_TS(9);
@@ -561,10 +555,7 @@ __global__ void __launch_bounds__(128 * (NQ + 1), 1)
             tmem_ld_wait();
             uint32_t o8[8];
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const float ha = unpack_lo<FMT>(h1p[c * 8 + i]), hb = unpack_hi<FMT>(h1p[c * 8 + i]);
-                o8[i] = pack2<FMT>(v[2 * i] * fmaf(-ha, ha, 1.0f), v[2 * i + 1] * fmaf(-hb, hb, 1.0f));
-            }
+            for (int i = 0; i < 8; i++) o8[i] = dtanh2<FMT>(v[2 * i], v[2 * i + 1], h1p[c * 8 + i]);
             *reinterpret_cast<uint4*>(xchunk(c * 2)) = make_uint4(o8[0], o8[1], o8[2], o8[3]);
             *reinterpret_cast<uint4*>(xchunk(c * 2 + 1)) = make_uint4(o8[4], o8[5], o8[6], o8[7]);
         }

@@ -762,18 +762,19 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
                         d[c * 4 + 2] = fmaf(dq, w.z, d[c * 4 + 2]); d[c * 4 + 3] = fmaf(dq, w.w, d[c * 4 + 3]);
                     }
                 }
+                uint4 dz[8];
 #pragma unroll
-                for (int c = 0; c < 8; c++) {   // h2 comes back from its 16-bit copy (this thread wrote it in P2)
-                    float h2[8];
-                    load8<FMT>(A2 + act_chunk_off(wt, c), h2);
-#pragma unroll
-                    for (int i = 0; i < 8; i++) d[c * 8 + i] *= fmaf(-h2[i], h2[i], 1.0f);
+                for (int c = 0; c < 8; c++) {   // h2 comes back from its 16-bit copy (this thread wrote it in P2); the
+                    // derivative factor and the product are formed on packed pairs (umma.cuh: dtanh2)
+                    const uint4 hq = *reinterpret_cast<const uint4*>(A2 + act_chunk_off(wt, c));
+                    dz[c].x = dtanh2<FMT>(d[c * 8 + 0], d[c * 8 + 1], hq.x); dz[c].y = dtanh2<FMT>(d[c * 8 + 2], d[c * 8 + 3], hq.y);
+                    dz[c].z = dtanh2<FMT>(d[c * 8 + 4], d[c * 8 + 5], hq.z); dz[c].w = dtanh2<FMT>(d[c * 8 + 6], d[c * 8 + 7], hq.w);
                 }
                 TC_TS(tsb + 15 + net * 4);
                 mbar_wait(doneW, (pw >> net) & 1u); pw ^= 1u << net;  // G5 has read A2 / DO
                 TC_TS(tsb + 16 + net * 4);
 #pragma unroll
-                for (int c = 0; c < 8; c++) store8<FMT>(A2 + act_chunk_off(wt, c), d + c * 8);
+                for (int c = 0; c < 8; c++) *reinterpret_cast<uint4*>(A2 + act_chunk_off(wt, c)) = dz[c];
                 fence_async_smem();
                 mbar_arrive(ready + net);
                 TC_TS(tsb + 17 + net * 4);
@@ -794,18 +795,18 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
 #pragma unroll
                 for (int c = 0; c < 4; c++) tmem_ld16(zaddr + c * 16, d + c * 16);
                 tmem_ld_wait();
+                uint4 dz[8];
 #pragma unroll
                 for (int c = 0; c < 8; c++) {
-                    float h1[8];
-                    load8<FMT>(A1 + act_chunk_off(wt, c), h1);
-#pragma unroll
-                    for (int i = 0; i < 8; i++) d[c * 8 + i] *= fmaf(-h1[i], h1[i], 1.0f);
+                    const uint4 hq = *reinterpret_cast<const uint4*>(A1 + act_chunk_off(wt, c));
+                    dz[c].x = dtanh2<FMT>(d[c * 8 + 0], d[c * 8 + 1], hq.x); dz[c].y = dtanh2<FMT>(d[c * 8 + 2], d[c * 8 + 3], hq.y);
+                    dz[c].z = dtanh2<FMT>(d[c * 8 + 4], d[c * 8 + 5], hq.z); dz[c].w = dtanh2<FMT>(d[c * 8 + 6], d[c * 8 + 7], hq.w);
                 }
                 TC_TS(tsb + 25 + net * 6);
                 mbar_wait(doneW, (pw >> net) & 1u); pw ^= 1u << net;  // G3 has read A1 / A2
                 TC_TS(tsb + 26 + net * 6);
 #pragma unroll
-                for (int c = 0; c < 8; c++) store8<FMT>(A2 + act_chunk_off(wt, c), d + c * 8);
+                for (int c = 0; c < 8; c++) *reinterpret_cast<uint4*>(A2 + act_chunk_off(wt, c)) = dz[c];
                 tc_fence_before();
                 fence_async_smem();
                 mbar_arrive(ready + net);
