@@ -124,8 +124,9 @@ constexpr int CAT_MAXKH_LIMIT = 8;
 template <int HP, int CAT_MAXKH>
 __global__ void __launch_bounds__(256) categorical_lane_kernel(const CatArgs a) {
     constexpr int RPW = 32 / HP;
-    const int lane = threadIdx.x & 31;
-    const int64_t row_base = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32;
+    __shared__ uint32_t us[8][32][PPO_MAX_HEADS + 1];   // per warp: the Philox words of its 32 rows (odd stride: no conflicts)
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t row_base = ((int64_t)blockIdx.x * (blockDim.x >> 5) + wib) * 32;
     if (row_base >= a.n) return;
     const int h = lane % HP, rl = lane / HP;
     const int heads = a.heads, K = a.K;
@@ -140,92 +141,89 @@ __global__ void __launch_bounds__(256) categorical_lane_kernel(const CatArgs a) 
     const bool philox = sample && a.uniforms == nullptr;
     const bool ref_quirk = !masked && a.entropy_mode == PPO_ENTROPY_REFERENCE;
 
-    uint32_t w[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // this lane's ROW (row_base + lane): uniforms of heads 0..7
-    if (philox && row_base + lane < a.n) {
-        uint32_t r[4];
-        Philox::gen(a.seed, (uint32_t)(row_base + lane), RNG_STREAM_SAMPLE, (uint32_t)a.counter, (uint32_t)(a.counter >> 32), r);
-        w[0] = r[0]; w[1] = r[1]; w[2] = r[2]; w[3] = r[3];
+    if (philox) {   // lane l draws the blocks of row (row_base + l) once; a pass reads its word back from shared memory
+        uint32_t r[4] = {0u, 0u, 0u, 0u};
+        const bool live = row_base + lane < a.n;
+        if (live)
+            Philox::gen(a.seed, (uint32_t)(row_base + lane), RNG_STREAM_SAMPLE, (uint32_t)a.counter, (uint32_t)(a.counter >> 32), r);
+        us[wib][lane][0] = r[0]; us[wib][lane][1] = r[1]; us[wib][lane][2] = r[2]; us[wib][lane][3] = r[3];
         if (heads > 4) {
-            Philox::gen(a.seed, (uint32_t)(row_base + lane), RNG_STREAM_SAMPLE | (1u << 8), (uint32_t)a.counter,
-                        (uint32_t)(a.counter >> 32), r);
-            w[4] = r[0]; w[5] = r[1]; w[6] = r[2]; w[7] = r[3];
+            if (live)
+                Philox::gen(a.seed, (uint32_t)(row_base + lane), RNG_STREAM_SAMPLE | (1u << 8), (uint32_t)a.counter,
+                            (uint32_t)(a.counter >> 32), r);
+            us[wib][lane][4] = r[0]; us[wib][lane][5] = r[1]; us[wib][lane][6] = r[2]; us[wib][lane][7] = r[3];
         }
+        __syncwarp();
     }
+    // the per-logit loops below are branch-free: a slot beyond the lane's head size carries x = -inf (e = p = 0) and
+    // every conditional is a select, so lanes with 2- and 3-logit heads run the same instruction stream
 #pragma unroll 1
     for (int p = 0; p < HP; p++) {
         const int r_local = p * RPW + rl;
         const int64_t row = row_base + r_local;
         const bool on = hon && row < a.n;
+        const int64_t base = on ? row * K + off : 0;
         float u = 0.0f;
-        if (philox) {
-            uint32_t uw = 0u;
-#pragma unroll
-            for (int hh = 0; hh < PPO_MAX_HEADS; hh++) {
-                const uint32_t t = __shfl_sync(0xffffffffu, w[hh], r_local);
-                if (hh == h) uw = t;
-            }
-            u = Philox::u01(uw);
-        } else if (sample && on) {
-            u = __ldg(a.uniforms + row * heads + h);
-        }
-        int pick = (!sample && on) ? __ldg(a.actions_in + row * heads + h) : -1;
+        if (philox) u = Philox::u01(us[wib][r_local][hon ? h : 0]);
+        else if (sample && on) u = __ldg(a.uniforms + row * heads + h);
+        const int given = (!sample && on) ? __ldg(a.actions_in + row * heads + h) : -1;
         float xm[CAT_MAXKH], e[CAT_MAXKH];
         uint32_t vbits = 0u;
-        const float* xp = a.logits + row * K + off;
-        const uint8_t* mp = a.mask + row * K + off;
         float mx = -INFINITY;
 #pragma unroll
         for (int j = 0; j < CAT_MAXKH; j++) {
-            xm[j] = -INFINITY;
-            if (on && j < Kh) {
-                const bool v = !masked || __ldg(mp + j) != 0;
-                xm[j] = v ? __ldg(xp + j) : -1e8f;      // CategoricalMasked.cpp:35
-                vbits |= (uint32_t)v << j;
-                mx = fmaxf(mx, xm[j]);
-            }
+            const bool in = on && j < Kh;
+            const int64_t idx = base + (in ? j : 0);
+            const float x = __ldg(a.logits + idx);
+            const bool v = in && (!masked || __ldg(a.mask + idx) != 0);
+            xm[j] = in ? (v ? x : -1e8f) : -INFINITY;      // CategoricalMasked.cpp:35
+            vbits |= (uint32_t)v << j;
+            mx = fmaxf(mx, xm[j]);
         }
+        mx = on ? mx : 0.0f;
         float sum = 0.0f;
 #pragma unroll
         for (int j = 0; j < CAT_MAXKH; j++) {
-            e[j] = 0.0f;
-            if (j < Kh) {
-                asm("ex2.approx.f32 %0, %1;" : "=f"(e[j]) : "f"((xm[j] - mx) * 1.4426950408889634f));
-                sum += e[j];
-            }
+            asm("ex2.approx.f32 %0, %1;" : "=f"(e[j]) : "f"((xm[j] - mx) * 1.4426950408889634f));
+            sum += e[j];
         }
+        sum = on ? sum : 1.0f;
         float rs, lg;
         asm("rcp.approx.f32 %0, %1;" : "=f"(rs) : "f"(sum));
         asm("lg2.approx.f32 %0, %1;" : "=f"(lg) : "f"(sum));
         const float lse = fmaf(lg, 0.6931471805599453f, mx);
-        float c = 0.0f, acc = 0.0f;
+        float c = 0.0f, acc = 0.0f, chi = 2.0f, clo = -1.0f;
         int last_valid = 0, apick = -1;
-        bool near = false;
 #pragma unroll
         for (int j = 0; j < CAT_MAXKH; j++) {
-            if (j < Kh) {
-                const float pj = e[j] * rs, lp = xm[j] - lse;
-                float t;
-                if (ref_quirk) {
-                    t = __fmul_rn(fmaxf(lp, FLT_MIN), pj);     // Categorical.cpp:114-117
-                } else {
-                    t = lp * pj;
-                    if (!((vbits >> j) & 1u) || pj == 0.0f) t = 0.0f;
-                }
-                acc += t;
-                if (pj > 0.0f) last_valid = j;
-                c += pj;
-                near = near || fabsf(u - c) < CAT_BAND;
-                if (apick < 0 && u < c) apick = j;
-                if (a.probs_out && on) a.probs_out[row * K + off + j] = pj;
-            }
+            const float pj = e[j] * rs, lp = xm[j] - lse;
+            const bool pos = pj > 0.0f;
+            float t = ref_quirk ? __fmul_rn(fmaxf(lp, FLT_MIN), pj) : lp * pj;
+            t = (ref_quirk ? j < Kh : (pos && ((vbits >> j) & 1u))) ? t : 0.0f;
+            acc += t;
+            last_valid = pos ? j : last_valid;
+            const float cn = c + pj;
+            const bool hit = apick < 0 && u < cn && j < Kh;
+            clo = hit ? c : clo;
+            chi = hit ? cn : chi;
+            apick = hit ? j : apick;
+            c = cn;
         }
+        if (a.probs_out && on) {
+#pragma unroll
+            for (int j = 0; j < CAT_MAXKH; j++)
+                if (j < Kh) a.probs_out[base + j] = e[j] * rs;
+        }
+        int pick = given;
         if (sample) {
             pick = apick < 0 ? last_valid : apick;
-            if (near && on) {   // within the band of a CDF edge: the oracle's IEEE operation order decides
+            // the draw decided between clo <= u < chi: closer than the band to either edge (or past the last edge), the
+            // oracle's IEEE operation order decides
+            const bool near = apick < 0 || chi - u < CAT_BAND || u - clo < CAT_BAND;
+            if (near && on) {
                 float mxe = -INFINITY;
 #pragma unroll
-                for (int j = 0; j < CAT_MAXKH; j++)
-                    if (j < Kh) mxe = fmaxf(mxe, xm[j]);
+                for (int j = 0; j < CAT_MAXKH; j++) mxe = fmaxf(mxe, xm[j]);
                 float se = 0.0f;
 #pragma unroll
                 for (int j = 0; j < CAT_MAXKH; j++)
@@ -246,8 +244,7 @@ __global__ void __launch_bounds__(256) categorical_lane_kernel(const CatArgs a) 
         }
         float lpa = 0.0f;
 #pragma unroll
-        for (int j = 0; j < CAT_MAXKH; j++)
-            if (j == pick) lpa = xm[j] - lse;
+        for (int j = 0; j < CAT_MAXKH; j++) lpa = j == pick ? xm[j] - lse : lpa;
         float lpr = on ? lpa : 0.0f, enr = on ? -acc : 0.0f;
 #pragma unroll
         for (int o = 1; o < HP; o <<= 1) {
