@@ -188,6 +188,36 @@ def test_categorical_sampling_vs_oracle(P, orc, n, nvec, masked):
     assert torch.equal(lp2, lp)
 
 
+@pytest.mark.parametrize("impl", [0, 1])
+def test_categorical_kernel_variants(P, orc, request, impl):
+    """both ppo_categorical kernels (0: IEEE row-per-thread, 1: (row, head) per lane = default)
+    against the oracle on the config-D shape: same actions outside the 2^-22 CDF band, log-prob / entropy / probs in bounds"""
+    lib = P.capi.load()
+    lib.ppo_debug_categorical_impl(impl)
+    request.addfinalizer(lambda: lib.ppo_debug_categorical_impl(1))
+    rng = np.random.default_rng(impl)
+    n, nvec = 20011, [3, 3, 3, 3, 3, 2, 2, 2]
+    K, heads = sum(nvec), len(nvec)
+    logits = (rng.standard_normal((n, K)) * 2).astype(np.float32)
+    mask = (rng.uniform(size=(n, K)) < 0.7).astype(np.uint8)
+    mask[:, np.cumsum([0] + nvec[:-1])] = 1
+    u = rng.uniform(size=(n, heads)).astype(np.float32)
+    a, lp, ent, probs = P.ops.categorical(dev(logits), nvec, mask=dev(mask), uniforms=dev(u), want_probs=True)
+    oa, olp, oent, oprobs, _ = orc.categorical(logits, nvec, mask=mask, uniforms=u, want_probs=True)
+    close(probs, oprobs, rtol=4e-6, atol=1e-9)
+    off, edge = 0, np.zeros((n, heads), bool)
+    for h, k in enumerate(nvec):
+        edge[:, h] = np.min(np.abs(np.cumsum(oprobs[:, off:off + k].astype(np.float64), 1) - u[:, h:h + 1]), 1) < 2.0 ** -22
+        off += k
+    diff = a.cpu().numpy() != oa
+    assert np.all(~diff | edge)
+    same = ~diff.any(1)
+    close(lp.cpu().numpy()[same], olp[same], rtol=1e-5, atol=4e-6)
+    close(ent.cpu().numpy()[same], oent[same], rtol=1e-5, atol=4e-6)
+    a2, lp2, _ = P.ops.categorical(dev(logits), nvec, mask=dev(mask), seed=5, counter=9)       # Philox path runs
+    assert np.all(mask[np.arange(n)[:, None], np.cumsum([0] + nvec[:-1])[None, :] + a2.cpu().numpy()] == 1)
+
+
 def test_categorical_philox_stream(P, orc):
     """without injected uniforms the kernel draws Philox(seed, row, counter, head): same actions as the oracle
     fed the numpy restatement of that stream."""
