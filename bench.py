@@ -41,7 +41,10 @@ REF_SAMPLE_ENVS = 32768   # env count the CPU arm runs when the workload itself 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE update-kernel launch from an `ncu --set full` capture of this
 # command (profiles/r01r_update_tc_ncu.txt, cold L2): 14.82 MB.  Algorithmic bytes per launch are 131072 rows x
 # 36 B = 4.7 MB, fetched as 64-byte packed records = 8.4 MB (ppo_pack_rows), + 37 KB of parameters per CTA.
-NCU_TRAFFIC = {("cartpole_4096x128_h64", 2): 14.82e6}
+NCU_TRAFFIC = {("cartpole_4096x128_h64", 2): 14.82e6,
+               # hidden = 256 (profiles/r02a_update_h256_ncu.txt): update_h256_kernel 1.04 GB read + 8.55 GB written (the fp16 h1 /
+               # dZ2 scratch of 4.19 M rows x 2 nets), dw2_h256_kernel 8.60 GB read + 0.07 GB written
+               ("mountaincar_65536x256_h256", 2): 18.25e9}
 HYPER = dict(gamma=0.98, gae_lambda=0.95, clip_coef=0.2, norm_adv=True, clip_vloss=True, ent_coef=0.0, vf_coef=0.5,
              max_grad_norm=0.5)
 LR0 = 1e-3
