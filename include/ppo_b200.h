@@ -38,7 +38,8 @@ extern "C" {
 #define PPO_MAX_LOGITS 64
 
 enum { PPO_OK = 0, PPO_ERR_ARG = 1, PPO_ERR_CUDA = 2, PPO_ERR_UNSUPPORTED = 3, PPO_ERR_COMM = 4 };
-enum { PPO_ENV_CARTPOLE = 0, PPO_ENV_MOUNTAINCAR = 1, PPO_ENV_MULTIWALK = 2 };
+enum { PPO_ENV_CARTPOLE = 0, PPO_ENV_MOUNTAINCAR = 1, PPO_ENV_MULTIWALK = 2,
+       PPO_ENV_HOST = 1000 /* environments stepped by the caller on the host (ppo_trainer_update) */ };
 /* PPO_ENTROPY_REFERENCE reproduces Distributions/Categorical.cpp:114-117 bit-for-bit in effect
  * (clamp min = FLT_MIN => entropy == -FLT_MIN*sum(p), zero gradient) for UNMASKED heads;
  * masked heads always use the correct formula (CategoricalMasked.cpp:140-142). */
@@ -322,6 +323,12 @@ void* ppo_trainer_buffer(ppo_trainer* t, const char* name, int64_t* bytes);
  * have been copied back (this call synchronises the stream once, at the end) unless
  * h_result is NULL (fully asynchronous). */
 int ppo_trainer_iterate(ppo_trainer* t, float h_lr, ppo_iter_result* h_result, ppo_stream_t stream);
+/* The part of an iteration behind the rollout, on rollout rows the CALLER filled through ppo_trainer_buffer ("obs",
+ * "actions", "logprobs", "rewards", "dones", "values", "next_value", "next_done"; optionally "fin_len" / "fin_ret" /
+ * "ep_stats"): calcAdvantage + E x MB optimiser steps + diagnostics (PPO/PPO_Discrete.cpp:556-673).  This is what a
+ * host-environment bridge calls (env_kind = PPO_ENV_HOST: PPO_Discrete.cpp:413-483 runs on the host, README "embed in game
+ * engines"); eager launches, h_result as in ppo_trainer_iterate. */
+int ppo_trainer_update(ppo_trainer* t, float h_lr, ppo_iter_result* h_result, ppo_stream_t stream);
 /* Split phases of one iteration, in the order iterate() issues them (for host loops that
  * interleave their own work, e.g. tests that inspect the rollout before the update). */
 int ppo_trainer_rollout(ppo_trainer* t, float h_lr, ppo_stream_t stream);

@@ -45,7 +45,8 @@ int ppo_debug_umma_time(int mode, int fmt, const float* A, const float* B, float
  * 8 logits; 0: the row-per-thread kernel (IEEE expf / logf / division per logit) for every shape. */
 int ppo_debug_categorical_impl(int impl);
 /* 1 (default): ppo_adv_stats_all_epochs reads the advantages in one coalesced pass per epoch through the inverse
- * permutation once there are at least 2^22 rows; 0: the permuted-gather kernel for every size. */
+ * permutation once there are at least 2^25 rows (beyond what stays L2-resident); 0: the permuted-gather kernel for every
+ * size; 2: the coalesced kernel for every size (at most 8 minibatches per epoch). */
 int ppo_debug_adv_impl(int impl);
 /* In-kernel timeline of update_h256_kernel: d_ts = device buffer of 64 int64 (NULL switches it off); later launches stamp the
  * SM clock of CTA 0 / thread 0 at 14 phase edges of its first 4 tiles, 16 slots per tile (tools/h256_timeline.py). */

@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libppo_b200.so")
 
 PPO_MAX_HEADS = 8
 ENV_CARTPOLE, ENV_MOUNTAINCAR, ENV_MULTIWALK = 0, 1, 2
+ENV_HOST = 1000
 ENTROPY_REFERENCE, ENTROPY_EXACT = 0, 1
 MATH_FP32, MATH_BF16, MATH_FP16 = 0, 1, 2
 
@@ -133,6 +134,7 @@ _PROTOS = {
     "ppo_trainer_reset_envs": (C.c_int, [_P]),
     "ppo_trainer_buffer": (_P, [_P, C.c_char_p, C.POINTER(C.c_int64)]),
     "ppo_trainer_iterate": (C.c_int, [_P, C.c_float, C.POINTER(IterResult), _P]),
+    "ppo_trainer_update": (C.c_int, [_P, C.c_float, C.POINTER(IterResult), _P]),
     "ppo_trainer_rollout": (C.c_int, [_P, C.c_float, _P]),
     "ppo_trainer_begin_epoch": (C.c_int, [_P, C.c_int, _P]),
     "ppo_trainer_minibatch_grads": (C.c_int, [_P, C.c_int, _P]),

@@ -155,7 +155,9 @@ extern "C" ppo_trainer* ppo_trainer_create(const ppo_trainer_cfg* c) {
     ppo_trainer* t = new ppo_trainer();
     t->cfg = *c;
     if (make_dims(&c->dims, &t->d)) { delete t; return nullptr; }
-    const int S = ppo_env_state_dim(c->env_kind);
+    // PPO_ENV_HOST: the environments live on the host (f4 bridge): no device env state is stepped, the caller fills the
+    // rollout rows and runs ppo_trainer_update
+    const int S = c->env_kind == PPO_ENV_HOST ? t->d.O : ppo_env_state_dim(c->env_kind);
     if (S < 0 || S != t->d.O) {
         set_error("ppo_trainer_create: env kind %d observes %d floats but obs_dim=%d", c->env_kind, S, t->d.O);
         delete t;
@@ -341,6 +343,7 @@ extern "C" int ppo_trainer_set_opt_state(ppo_trainer* t, const float* m, const f
 // initEnvs (PPO_Discrete.cpp:365-402): reset every env; next_done = 0 (:502)
 extern "C" int ppo_trainer_reset_envs(ppo_trainer* t) {
     PPO_REQUIRE(t, "null trainer");
+    if (t->cfg.env_kind == PPO_ENV_HOST) return PPO_OK;   // nothing on the device to reset
     const int N = t->cfg.num_envs;
     // env RNG key = global env index; ppo_env_reset keys on the local index, so offset the seed stream
     // through the counter: use the dedicated init counter ~0 and a rank-salted seed.
@@ -374,8 +377,14 @@ extern "C" int ppo_debug_pack_rows(int on) {
     return PPO_OK;
 }
 
-static int phase_rollout(ppo_trainer* t, cudaStream_t st) {
+static int phase_rollout(ppo_trainer* t, cudaStream_t st, bool external = false) {
     const ppo_trainer_cfg& c = t->cfg;
+    if (external) {   // the rollout rows, next_value / next_done (and ep_stats / the episode log) were filled by the caller
+        PhaseTimer pt(t, PH_GAE, st);
+        return ppo_gae(c.num_steps, c.num_envs, t->rewards, t->values, t->dones, t->next_value, t->next_done, c.gamma,
+                       c.gae_lambda, c.use_gae, t->adv, t->ret, st);
+    }
+    PPO_REQUIRE(c.env_kind != PPO_ENV_HOST, "host environments: fill the rollout rows and call ppo_trainer_update");
     PPO_CUDA(cudaMemsetAsync(t->ep_stats, 0, 3 * 8, st));
     ppo_rollout_cfg rc{};
     rc.env_kind = c.env_kind; rc.n_envs = c.num_envs; rc.n_steps = c.num_steps;
@@ -507,10 +516,10 @@ static int phase_tail(ppo_trainer* t, cudaStream_t st) {
     return PPO_OK;
 }
 
-static int enqueue_iteration(ppo_trainer* t, cudaStream_t st) {
+static int enqueue_iteration(ppo_trainer* t, cudaStream_t st, bool external_rollout = false) {
     int rc;
     t->opt_in_iter = 0;
-    if ((rc = phase_rollout(t, st))) return rc;
+    if ((rc = phase_rollout(t, st, external_rollout))) return rc;
     const bool dp = t->cfg.world_size > 1 && t->comm;
     // world_size > 1 needs a transport: the NCCL communicator (advantage moments, and gradients without peer memory)
     PPO_REQUIRE(t->cfg.world_size == 1 || t->comm,
@@ -569,6 +578,27 @@ static void fill_result(ppo_trainer* t, float lr, ppo_iter_result* r) {
     r->ep_len_sum = t->h_rb->ep_stats[1];
     r->ep_ret_sum = t->h_rb->ep_stats[2];
     r->lr = lr;
+}
+
+// Everything of an iteration BEHIND the rollout, on rollout rows the caller filled (obs, actions, logprobs, rewards, dones,
+// values [T, N ..], next_value, next_done [N], optionally fin_len / fin_ret / ep_stats): calcAdvantage + the E x MB optimiser
+// steps + diagnostics (PPO_Discrete.cpp:556-673).  For host-side environments (f4) and callers with their own rollout.
+extern "C" int ppo_trainer_update(ppo_trainer* t, float h_lr, ppo_iter_result* h_result, ppo_stream_t stream) {
+    PPO_REQUIRE(t, "null trainer");
+    cudaStream_t st = as_stream(stream);
+    int rc;
+    if ((rc = push_scalars(t, h_lr, st))) return rc;
+    if ((rc = enqueue_iteration(t, st, true))) return rc;
+    advance_counters(t);
+    if (h_result) {
+        PPO_CUDA(cudaStreamSynchronize(st));
+        fill_result(t, h_lr, h_result);
+        if (t->h_rb->peer_err) {
+            set_error("an in-kernel wait ran out: the optimiser steps from there on were skipped");
+            return PPO_ERR_COMM;
+        }
+    }
+    return PPO_OK;
 }
 
 extern "C" int ppo_trainer_iterate(ppo_trainer* t, float h_lr, ppo_iter_result* h_result, ppo_stream_t stream) {

@@ -41,22 +41,15 @@ void PPOTrainerBase::build() {
     if (!m_use_cuda) throw std::runtime_error("use_cuda = false: the B200 path has no CPU fallback (run the reference's CPU path)");
     if (ppo_device_count() <= 0) throw std::runtime_error("no CUDA device visible: the B200 path has no CPU fallback");
     std::string env = m_config.env.empty() ? (m_multidiscrete ? "mountaincar" : "cartpole") : m_config.env;
-    // the environment registry (csrc/env.cuh: PPO_ENV_LIST) resolves the name; the reference fixes the env by the element
-    // type of m_envs (PPO/PPO_Discrete.h:106)
-    const int kind = ppo_env_kind_from_name(env.c_str());
-    if (kind < 0) {
-        std::string known;
-        for (int k = 0; ppo_env_name(k); k++) known += std::string(k ? ", " : "") + "\"" + ppo_env_name(k) + "\"";
-        throw std::runtime_error("[b200] env = \"" + env + "\": not a registered environment (" + known + ")");
-    }
-    if (ppo_env_state_dim(kind) != m_obs_size)   // initEnvs' size check (PPO_Discrete.cpp:370-375)
+    const int kind = deviceEnvKind(env);
+    if (kind != PPO_ENV_HOST && ppo_env_state_dim(kind) != m_obs_size)   // initEnvs' size check (PPO_Discrete.cpp:370-375)
         throw std::runtime_error("obs_size " + std::to_string(m_obs_size) + " does not match the environment's observation (" +
                                  std::to_string(ppo_env_state_dim(kind)) + " floats)");
     // action space: one head of action_size logits (Agent.cpp:21) unless PPO_MultiDiscrete is given the
     // MultiDiscrete nvec the reference keeps commented at Agent.cpp:16 through `[b200] nvec = [..]`
     std::vector<int64_t> nvec = {m_action_size};
     if (m_multidiscrete && !m_config.nvec.empty()) nvec = m_config.nvec;
-    if ((int)nvec.size() < ppo_env_num_heads(kind))
+    if (kind != PPO_ENV_HOST && (int)nvec.size() < ppo_env_num_heads(kind))
         throw std::runtime_error("environment \"" + env + "\" consumes " + std::to_string(ppo_env_num_heads(kind)) +
                                  " sub-actions per step: give PPO_MultiDiscrete its action space with [b200] nvec = [..]");
     if (nvec.size() > PPO_MAX_HEADS) throw std::runtime_error("[b200] nvec: at most " + std::to_string(PPO_MAX_HEADS) + " heads");
@@ -158,14 +151,30 @@ void PPOTrainerBase::saveCheckpoint(const std::string& agent_file, const std::st
     checkpoint_save_optimizer(m_shell, optimizer_file);
 }
 
-ppo_iter_result PPOTrainerBase::iterate(float lr) {
-    ppo_iter_result r{};
+// the environment registry (csrc/env.cuh: PPO_ENV_LIST) resolves the name; the reference fixes the env by the element type
+// of m_envs (PPO/PPO_Discrete.h:106)
+int PPOTrainerBase::deviceEnvKind(const std::string& env) const {
+    const int kind = ppo_env_kind_from_name(env.c_str());
+    if (kind < 0) {
+        std::string known;
+        for (int k = 0; ppo_env_name(k); k++) known += std::string(k ? ", " : "") + "\"" + ppo_env_name(k) + "\"";
+        throw std::runtime_error("[b200] env = \"" + env + "\": not a registered environment (" + known + ")");
+    }
+    return kind;
+}
+
+void* PPOTrainerBase::ensureStream() {
     if (!m_stream) {   // graph capture cannot run on the legacy default stream
         cudaStream_t st = nullptr;
         if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) throw std::runtime_error("cudaStreamCreate failed");
         m_stream = st;
     }
-    check(ppo_trainer_iterate(m_b200, lr, &r, m_stream), "ppo_trainer_iterate");
+    return m_stream;
+}
+
+ppo_iter_result PPOTrainerBase::iterate(float lr) {
+    ppo_iter_result r{};
+    check(ppo_trainer_iterate(m_b200, lr, &r, ensureStream()), "ppo_trainer_iterate");
     m_last_lr = lr;   // what the reference's optimizer holds when it is saved (lr_now, PPO_Discrete.cpp:514-518)
     return r;
 }
@@ -259,7 +268,7 @@ void PPOTrainerBase::train() {
         // Episode statistics (PPO_Discrete.cpp:474-480): the rollout kernel logs every finished episode at its (step, env)
         // slot, ppo_episode_tail compacts the newest 100 on the device, and they are pushed oldest first - the ring ends
         // up holding exactly what the reference's per-step pushes would have left in it.
-        {
+        if (!pushesEpisodeStats()) {
             int32_t lens[PPO_EPISODE_TAIL];
             float rets[PPO_EPISODE_TAIL];
             const int n = ppo_trainer_last_episodes(m_b200, PPO_EPISODE_TAIL, lens, rets);

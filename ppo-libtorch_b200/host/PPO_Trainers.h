@@ -34,8 +34,11 @@ public:
     void saveCheckpoint(const std::string& agent_file, const std::string& optimizer_file);
     void printPPOResults(int64_t update, int64_t global_step, std::chrono::milliseconds fps,
                          std::chrono::milliseconds time_elapsed, const ppo_iter_result& r);
-    // one PPO update (rollout + GAE + all optimiser steps) at learning rate lr; what train() loops over
-    ppo_iter_result iterate(float lr);
+    // one PPO update (rollout + GAE + all optimiser steps) at learning rate lr; what train() loops over.  Virtual: the
+    // host-environment bridge (PPO_HostEnv.h) runs the rollout on the host and only the update on the device.
+    virtual ppo_iter_result iterate(float lr);
+    // true: finished episodes are pushed into m_episode_stats by iterate() itself (host envs), not read from the device log
+    virtual bool pushesEpisodeStats() const { return false; }
     std::vector<float> getParameters() const;          // flat slab, reference registration order
     ppo_trainer* handle() const { return m_b200; }
     bool multidiscrete() const { return m_multidiscrete; }
@@ -65,6 +68,9 @@ public:
 protected:
     PPOTrainerBase(bool multidiscrete, const std::string& config_path);
     void build();                                      // agent shell, device trainer, resume
+    virtual int deviceEnvKind(const std::string& env_name) const;   // registry lookup; the host bridge returns PPO_ENV_HOST
+    void* ensureStream();
+    void noteLearningRate(float lr) { m_last_lr = lr; }   // what a checkpoint records as the optimizer's lr
 
 private:
     bool m_multidiscrete;

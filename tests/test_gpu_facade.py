@@ -235,3 +235,19 @@ def test_multidiscrete_facade_runs_the_masked_multihead_env(exe, tmp_path):
         f.write(MULTIWALK_TOML.format(total=4096).replace('"multiwalk"', '"pong"'))
     p = subprocess.run([exe, "multidiscrete"], cwd=tmp_path, capture_output=True, text=True, timeout=120)
     assert p.returncode == 1 and "not a registered environment" in p.stdout and "multiwalk" in p.stdout
+
+
+def test_host_env_bridge_trains_a_host_side_cartpole(tmp_path):
+    """host/hostenv_check.cpp defines a CartPole against the reference's literal host interface (reset() /
+    step(const int64_t&) / episode_length / episode_reward) and trains it through PPO_DiscreteHostEnv<Env>: environments on a
+    host thread pool, policy forward and the whole update on the GPU (ppo_trainer_update)."""
+    exe_path = os.path.join(ROOT, "ppo-libtorch_b200", "ppo_hostenv_check")
+    assert os.path.exists(exe_path), "ppo-libtorch_b200/ppo_hostenv_check is not built"
+    toml = TOML.format(total=100 * 32 * 32, cuda="true").replace("num_envs = 64", "num_envs = 32").replace(
+        "checkpoint_updates = 2", "checkpoint_updates = 1000")
+    with open(tmp_path / "PPOConfig.toml", "w") as f:
+        f.write(toml)
+    p = subprocess.run([exe_path], cwd=tmp_path, capture_output=True, text=True, timeout=900)
+    assert p.returncode == 0 and "hostenv_check: all ok" in p.stdout, p.stdout[-3000:] + p.stderr[-2000:]
+    assert "ok stepEnvs through the pinned staging buffers" in p.stdout
+    assert p.stdout.count("|    total_timesteps      | ") == 99
