@@ -184,12 +184,14 @@ __device__ __forceinline__ float unpack_hi(uint32_t v) {
 // single 16-bit rounding it gets when it is stored as a GEMM operand anyway.
 template <int FMT>
 __device__ __forceinline__ uint32_t dtanh2(float d_lo, float d_hi, uint32_t h) {
-    const uint32_t d = pack2<FMT>(d_lo, d_hi), nh = h ^ 0x80008000u;
-    uint32_t g, r;
+    const uint32_t d = pack2<FMT>(d_lo, d_hi);
+    uint32_t nh, g, r;   // neg (not an xor) so that ptxas folds it into the HFMA2 operand modifier
     if constexpr (FMT == FMT_BF16) {
+        asm("neg.bf16x2 %0, %1;" : "=r"(nh) : "r"(h));
         asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(g) : "r"(nh), "r"(h), "r"(0x3F803F80u));
         asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(d), "r"(g));
     } else {
+        asm("neg.f16x2 %0, %1;" : "=r"(nh) : "r"(h));
         asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(g) : "r"(nh), "r"(h), "r"(0x3C003C00u));
         asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(d), "r"(g));
     }

@@ -85,10 +85,14 @@ struct H256Args {
 // optional in-kernel timeline (ppo_debug_h256_timeline): SM clock stamps of CTA 0, thread 0 at the phase edges of its
 // first 4 tiles, 16 slots per tile (tools/h256_timeline.py prints the deltas)
 __device__ long long* g_h256_ts = nullptr;
+#ifdef PPO_TC_TIMELINE   // make TIMELINE=1
 #define H_TS(slot)                                                                        \
     do {                                                                                  \
         if (ts_buf && tile_no < 4) ts_buf[tile_no * 16 + (slot)] = clock64();             \
     } while (0)
+#else
+#define H_TS(slot) do { } while (0)
+#endif
 
 // tensor-memory map of update_h256_kernel: Z (forward pre-activations, then dX) in columns 0..255; the skinny
 // accumulators, 16 columns each, at 256 + 16 * (moment * 2 + jb): moment 0 = X holds h2 (cols 0..K-1 = dW3^T),
@@ -321,6 +325,7 @@ __global__ void __launch_bounds__(128 * (NQ + 1), 1)
     const float rstd = __fdividef(1.0f, stdf + 1e-8f);
 
     long long* ts_buf = (blockIdx.x == 0 && tid == 0) ? g_h256_ts : nullptr;
+    (void)ts_buf;
     int tile_no = -1;
     RowIn nxt = gather(cta);
     bool pendingW = false;   // G4 of the previous tile still reads X / NB

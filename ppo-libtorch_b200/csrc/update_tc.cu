@@ -86,10 +86,16 @@ __host__ __device__ inline TcLayout tc_layout(int K, int nwg) {
 // optional in-kernel timeline (ppo_debug_tc_timeline): SM clock stamps of CTA 0, thread `who`, slot-indexed
 __device__ long long* g_tc_ts = nullptr;
 __device__ int g_tc_ts_who = 0;
+// compiled in with -DPPO_TC_TIMELINE only (make TIMELINE=1): ~40 clock reads + predicated stores per tile were 4 % of the
+// kernel's executed instructions (CS2R 144 per row in profiles/r02b_update_tc_E_ncu.txt)
+#ifdef PPO_TC_TIMELINE
 #define TC_TS(slot)                                                                       \
     do {                                                                                  \
         if (ts_buf && (slot) < 256) ts_buf[(slot)] = clock64();                           \
     } while (0)
+#else
+#define TC_TS(slot) do { } while (0)
+#endif
 
 __device__ __forceinline__ float tanh_fast(float x) {
     float y;
@@ -378,6 +384,7 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
     const int ntiles = (a.mb_size + TC_ROWS - 1) / TC_ROWS;
     const int nthreads = (NWG + 1) * 128;   // NWG compute warpgroups + the MMA-issue warpgroup
     long long* ts_buf = (blockIdx.x == 0 && tid == (g_tc_ts_who & 0xFFFF)) ? g_tc_ts : nullptr;
+    (void)ts_buf;
     // who | 0x40000000: thread 0 of EVERY CTA also stamps the global timer (ns) at entry / exit into slots 256 + 2 b + {0, 1}
     long long* cta_ts = (g_tc_ts && (g_tc_ts_who & 0x40000000) && tid == 0) ? g_tc_ts + 256 + 2 * blockIdx.x : nullptr;
     if (cta_ts) { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); cta_ts[0] = t; }
@@ -639,6 +646,7 @@ __global__ void __launch_bounds__((NWG + 1) * 128, 1) update_tc_kernel(const Upd
             const bool on = cur.on;
             const int64_t r = cur.r;
             const int tsb = 8 + tiles_done * 40;
+            (void)tsb;
             TC_TS(tsb);
             const int par = tiles_done & 1;      // XE is double-buffered: G3b / G4 of the previous tile may still read it
             tiles_done++;
