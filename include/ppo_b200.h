@@ -256,6 +256,18 @@ int ppo_clip_adamw(float* params, float* grads, float* exp_avg, float* exp_avg_s
 int64_t ppo_explained_variance_workspace_bytes(void);
 int ppo_explained_variance(int64_t n, const float* returns, const float* values, void* workspace,
                            float* out, ppo_stream_t stream);
+/* No counterpart in the reference: added for callers that cannot allocate
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The same kernel and the
+ * same result as ppo_explained_variance, with the scratch (per-CTA partial moments + arrival ticket, 32 784 bytes)
+ * in a file-scope static __device__ array of the library: every GPU that loads the library holds it until exit, and
+ * the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine; one 16-byte cudaMemsetAsync of
+ * the ticket + one kernel on `stream`).  Limit: n <= PPO_EV_STATIC_MAX_N rows, larger n => PPO_ERR_ARG with a message
+ * (the workspace variant above has no such limit).  ALL calls on a device share the one array: calls that overlap
+ * on the GPU (different streams, no dependency between them) race on it — serialise them. */
+#define PPO_EV_STATIC_MAX_N ((int64_t)1 << 28)
+int64_t ppo_explained_variance_static_max_n(void);
+int ppo_explained_variance_static(int64_t n, const float* returns, const float* values, float* out,
+                                  ppo_stream_t stream);
 
 /* ---- minibatch permutation (replaces torch::randperm, PPO/PPO_Discrete.cpp:569) ----------- */
 /* Counter-based bijection on [0,batch): perm_out[i] = pi_{seed,epoch}(i).  d_epoch: optional

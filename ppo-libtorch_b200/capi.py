@@ -124,6 +124,8 @@ _PROTOS = {
                                  C.c_float, C.c_int64, _P, C.c_float, C.c_float, _P, _P]),
     "ppo_explained_variance_workspace_bytes": (C.c_int64, []),
     "ppo_explained_variance": (C.c_int, [C.c_int64, _P, _P, _P, _P, _P]),
+    "ppo_explained_variance_static_max_n": (C.c_int64, []),
+    "ppo_explained_variance_static": (C.c_int, [C.c_int64, _P, _P, _P, _P]),
     "ppo_make_permutation": (C.c_int, [C.c_int64, C.c_uint64, C.c_uint64, _P, _P, _P]),
     "ppo_trainer_create": (_P, [C.POINTER(TrainerCfg)]),
     "ppo_trainer_destroy": (None, [_P]),

@@ -3,6 +3,8 @@
 //   ppo_adv_stats(_finalize) per-minibatch advantage mean / unbiased std (:591-594)
 //   ppo_explained_variance  1 - var(R - V)/var(R)                   (:647-648)
 //   ppo_make_permutation    counter-based replacement of torch::randperm (:569)
+#include <mutex>
+
 #include "common.cuh"
 
 namespace ppo {
@@ -490,6 +492,62 @@ extern "C" int ppo_explained_variance(int64_t n, const float* returns, const flo
     if (blocks > EV_MAX_BLOCKS) blocks = EV_MAX_BLOCKS;
     double* part = reinterpret_cast<double*>(workspace);
     unsigned int* ticket = reinterpret_cast<unsigned int*>(part + (size_t)EV_MAX_BLOCKS * 4);
+    explained_variance_kernel<<<(int)blocks, EV_THREADS, 0, as_stream(stream)>>>(n, returns, values, part, ticket, out);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// ppo_explained_variance_static: the same kernel with its scratch (per-CTA partial moments + the arrival ticket) in
+// a file-scope device array instead of a caller-allocated workspace, for callers that may not allocate (stream
+// capture, serving loops).  No reference counterpart.
+// Every GPU that loads the library holds these 32 784 bytes until exit.  ALL calls on a device share the array:
+// calls that overlap on the GPU (different streams) race on it.
+constexpr size_t EV_STATIC_BYTES = (size_t)EV_MAX_BLOCKS * 4 * sizeof(double) + 16;
+static __device__ __align__(256) unsigned char g_ev_static_scratch[EV_STATIC_BYTES];
+constexpr int EV_STATIC_MAX_DEVICES = 64;
+
+// In host code `g_ev_static_scratch` is only a stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, resolved once per device with that device current.
+static int ev_static_scratch_ptr(void** out) {
+    static std::mutex mu;
+    static void* cached[EV_STATIC_MAX_DEVICES] = {};
+    int dev = -1;
+    PPO_CUDA(cudaGetDevice(&dev));
+    PPO_REQUIRE(dev >= 0 && dev < EV_STATIC_MAX_DEVICES, "ppo_explained_variance_static: device ordinal %d out of [0,%d)",
+                dev, EV_STATIC_MAX_DEVICES);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[dev]) {
+        void* p = nullptr;
+        PPO_CUDA(cudaGetSymbolAddress(&p, g_ev_static_scratch));
+        PPO_REQUIRE(p != nullptr, "ppo_explained_variance_static: cudaGetSymbolAddress returned NULL");
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return PPO_OK;
+}
+
+extern "C" int64_t ppo_explained_variance_static_max_n(void) { return PPO_EV_STATIC_MAX_N; }
+
+extern "C" int ppo_explained_variance_static(int64_t n, const float* returns, const float* values, float* out,
+                                             ppo_stream_t stream) {
+    PPO_REQUIRE(n >= 2 && returns && values && out, "ppo_explained_variance_static: bad arguments");
+    PPO_REQUIRE(n <= PPO_EV_STATIC_MAX_N,
+                "ppo_explained_variance_static: n=%lld exceeds the static-scratch variant's maximum of %lld rows "
+                "(use ppo_explained_variance with a caller-allocated workspace)",
+                (long long)n, (long long)PPO_EV_STATIC_MAX_N);
+    void* scratch = nullptr;
+    const int rc = ev_static_scratch_ptr(&scratch);
+    if (rc != PPO_OK) return rc;
+    const int sms = sm_count() > 0 ? sm_count() : 148;
+    int64_t blocks = (n + EV_THREADS * 8 - 1) / (EV_THREADS * 8);
+    if (blocks > 4 * sms) blocks = 4 * sms;
+    if (blocks > EV_MAX_BLOCKS) blocks = EV_MAX_BLOCKS;
+    double* part = reinterpret_cast<double*>(scratch);
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(part + (size_t)EV_MAX_BLOCKS * 4);
+    // the array keeps the last call's contents: the partials are overwritten before they are read, the ticket must
+    // start at zero (the kernel re-arms it, but a call that was aborted mid-flight would not have)
+    PPO_CUDA(cudaMemsetAsync(ticket, 0, 16, as_stream(stream)));
     explained_variance_kernel<<<(int)blocks, EV_THREADS, 0, as_stream(stream)>>>(n, returns, values, part, ticket, out);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
