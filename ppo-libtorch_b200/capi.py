@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libppo_b200.so")
+LIB_PATH = os.environ.get("PPO_B200_LIB") or os.path.join(_HERE, "libppo_b200.so")   # override: A/B runs of a saved build
 
 PPO_MAX_HEADS = 8
 ENV_CARTPOLE, ENV_MOUNTAINCAR, ENV_MULTIWALK = 0, 1, 2
