@@ -40,6 +40,10 @@ int ppo_debug_rollout_timeline(long long* d_ts);
 int ppo_debug_tc_timeline(long long* d_ts, int who);
 int ppo_debug_umma_time(int mode, int fmt, const float* A, const float* B, float* D, int reps, long long* d_cycles,
                         ppo_stream_t stream);
+/* tcgen05.mma throughput / concurrency probe (tools/umma_conc.py): `nwarps` warps each issue reps x 8 MMAs of one shape
+ * (0 M128N64 K/K, 1 M64N64 MN/MN, 2 M64N8 MN/narrow, 3 M128N8 MN/narrow, 4 M128N64 K/MN) from their own tiles into their
+ * own tensor-memory columns; d_cycles[0] = SM cycles from the first issue to the last completion. */
+int ppo_debug_umma_conc(int shape, int nwarps, int reps, long long* d_cycles, ppo_stream_t stream);
 
 /* 1 (default): ppo_categorical runs the warp-cooperative kernel (one (row, head) per lane) whenever every head has at most
  * 8 logits; 0: the row-per-thread kernel (IEEE expf / logf / division per logit) for every shape. */

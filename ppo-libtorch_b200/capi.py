@@ -155,6 +155,7 @@ _PROTOS = {
     "ppo_debug_umma_probe": (C.c_int, [C.c_int, C.c_int, _P, _P, _P, _P]),
     "ppo_debug_tc_timeline": (C.c_int, [_P, C.c_int]),
     "ppo_debug_umma_time": (C.c_int, [C.c_int, C.c_int, _P, _P, _P, C.c_int, _P, _P]),
+    "ppo_debug_umma_conc": (C.c_int, [C.c_int, C.c_int, C.c_int, _P, _P]),
 }
 EXPORTS = sorted(_PROTOS)
 

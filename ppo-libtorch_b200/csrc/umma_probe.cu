@@ -92,6 +92,83 @@ __global__ void __launch_bounds__(128) umma_probe_kernel(int mode, const float* 
     if (warp == 0) tmem_dealloc(tm, 64);
 }
 
+
+// Throughput / concurrency probe: `nw` warps (one per scheduler and beyond) each issue `reps` x 8 tcgen05.mma of one shape
+// from their own shared-memory tiles into their own tensor-memory columns, descriptors warp-uniform as in update_tc.cu.
+// cycles[0] = first issue -> last completion seen by warp 0's lane 0 after every warp's commit has arrived.
+//   shape 0: M128 N64, A K-major, B K-major      (G1)        1: M64 N64, A MN-major, B MN-major (dW2)
+//   shape 2: M64 N8, A MN-major, B narrow        (G3b/G4/G5)  3: M128 N8, A MN-major over two adjacent tiles, B narrow
+//   shape 4: M128 N64, A K-major, B MN-major     (G2)
+template <int FMT>
+__global__ void __launch_bounds__(256) umma_conc_kernel(int shape, int nw, int reps, long long* __restrict__ cycles) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    __shared__ uint64_t bar[8];
+    __shared__ uint32_t tmem_base_s;
+    const int t = threadIdx.x, warp = t >> 5;
+    if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+    if (t == 0) {
+        for (int i = 0; i < 8; i++) mbar_init(bar + i, 1);
+        mbar_init_fence();
+    }
+    for (int i = t; i < 8 * 24576 / 4; i += 256) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;   // fp16 ones
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tm = tmem_base_s;
+    long long t0 = clock64();
+    if (warp < nw) {
+        const uint32_t a = __shfl_sync(0xffffffffu, smem_u32(smem + warp * 24576), 0);   // 16 KB A tile (+ 8 KB B)
+        const uint32_t b = a + 16384;
+        const uint32_t d = tm + (uint32_t)warp * 64u;
+        const bool lead = elect_one();
+        for (int rep = 0; rep < reps; rep++) {
+            if (shape == 0) {
+                constexpr uint32_t id = idesc_f16(FMT, 128, 64, 0, 0);
+                const uint64_t da = act_desc_kmajor(a, 0), db = act_desc_kmajor(b, 0);
+                if (lead)
+#pragma unroll
+                    for (int ks = 0; ks < 8; ks++) mma_f16(d, da + 2u * (ks & 3), db + 2u * (ks & 3), id, 1u);
+            } else if (shape == 1) {
+                constexpr uint32_t id = idesc_f16(FMT, 64, 64, 1, 1);
+                const uint64_t da = act_desc_mnmajor(a, 0), db = act_desc_mnmajor(b, 0);
+                if (lead)
+#pragma unroll
+                    for (int ks = 0; ks < 8; ks++) mma_f16(d, da + 128u * (ks & 3), db + 128u * (ks & 3), id, 1u);
+            } else if (shape == 2) {
+                constexpr uint32_t id = idesc_f16(FMT, 64, 8, 1, 1);
+                const uint64_t da = act_desc_mnmajor(a, 0), db = narrow_desc_mnmajor(b, 128, 0);
+                if (lead)
+#pragma unroll
+                    for (int ks = 0; ks < 8; ks++) mma_f16(d, da + 128u * ks, db + 16u * ks, id, 1u);
+            } else if (shape == 3) {
+                constexpr uint32_t id = idesc_f16(FMT, 128, 8, 1, 1);
+                const uint64_t da = smem_desc(a, 8192, 1024, LAYOUT_SW128), db = narrow_desc_mnmajor(b, 128, 0);
+                if (lead)
+#pragma unroll
+                    for (int ks = 0; ks < 8; ks++) mma_f16(d, da + 128u * (ks & 3), db + 16u * ks, id, 1u);
+            } else {
+                constexpr uint32_t id = idesc_f16(FMT, 128, 64, 0, 1);
+                const uint64_t da = act_desc_kmajor(a, 0), db = act_desc_mnmajor(b, 0);
+                if (lead)
+#pragma unroll
+                    for (int ks = 0; ks < 8; ks++) mma_f16(d, da + 2u * (ks & 3), db + 128u * (ks & 3), id, 1u);
+            }
+            __syncwarp();
+        }
+        if (lead) mma_commit(bar + warp);
+        __syncwarp();
+    }
+    if (warp == 0) {
+        for (int w = 0; w < nw; w++) mbar_wait(bar + w, 0);
+        if (t == 0 && cycles) cycles[0] = clock64() - t0;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tm, 512);
+}
+
 }  // namespace ppo
 
 static int probe_launch(int mode, int fmt, const float* A, const float* B, float* D, int reps, long long* cycles,
@@ -115,6 +192,19 @@ static int probe_launch(int mode, int fmt, const float* A, const float* B, float
     }
     if (fmt == 0) umma_probe_kernel<0><<<1, 128, 40960, as_stream(stream)>>>(mode, A, B, D, reps, cycles);
     else umma_probe_kernel<1><<<1, 128, 40960, as_stream(stream)>>>(mode, A, B, D, reps, cycles);
+    PPO_LAUNCH_CHECK();
+    return PPO_OK;
+}
+
+extern "C" int ppo_debug_umma_conc(int shape, int nwarps, int reps, long long* d_cycles, ppo_stream_t stream) {
+    using namespace ppo;
+    PPO_REQUIRE(shape >= 0 && shape <= 4 && nwarps >= 1 && nwarps <= 8 && reps >= 1, "ppo_debug_umma_conc: bad argument");
+    static bool attr_done = false;
+    if (!attr_done) {
+        PPO_CUDA(cudaFuncSetAttribute(umma_conc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 24576 + 1024));
+        attr_done = true;
+    }
+    umma_conc_kernel<0><<<1, 256, 8 * 24576 + 1024, as_stream(stream)>>>(shape, nwarps, reps, d_cycles);
     PPO_LAUNCH_CHECK();
     return PPO_OK;
 }
