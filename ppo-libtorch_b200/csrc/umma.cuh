@@ -198,5 +198,30 @@ __device__ __forceinline__ uint32_t dtanh2(float d_lo, float d_hi, uint32_t h) {
     return r;
 }
 
+// packed 16-bit pair arithmetic (one instruction for two elements)
+template <int FMT>
+__device__ __forceinline__ uint32_t hmul2(uint32_t a, uint32_t b) {
+    uint32_t r;
+    if constexpr (FMT == FMT_BF16) asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    else asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+template <int FMT>
+__device__ __forceinline__ uint32_t hfma2(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    if constexpr (FMT == FMT_BF16) asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    else asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+// dtanh2 for an upstream gradient that is already a packed pair: d * (1 - h^2)
+template <int FMT>
+__device__ __forceinline__ uint32_t dtanh2p(uint32_t d, uint32_t h) {
+    uint32_t nh;
+    if constexpr (FMT == FMT_BF16) asm("neg.bf16x2 %0, %1;" : "=r"(nh) : "r"(h));
+    else asm("neg.f16x2 %0, %1;" : "=r"(nh) : "r"(h));
+    const uint32_t one = FMT == FMT_BF16 ? 0x3F803F80u : 0x3C003C00u;
+    return hmul2<FMT>(d, hfma2<FMT>(nh, h, one));
+}
+
 }  // namespace umma
 }  // namespace ppo

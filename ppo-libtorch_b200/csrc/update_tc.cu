@@ -50,6 +50,7 @@ struct TcLayout {   // byte offsets into the 1024-aligned dynamic shared memory
     TC_PAIR(xe)      // (tile parity): 16-bit {obs, 1, 0..} (hi) then its residual (lo)
     TC_PAIR(p1h)     // 16-bit P1 = {W1|b1|0} as K chunks {hi, hi, lo, 0} [4][64 units][8]: B of the layer-1 MMAs
     TC_PAIR(b2) TC_PAIR(w3) TC_PAIR(b3p)    // fp32 small parameters per net
+    TC_PAIR(w3h)     // W3 as packed 16-bit pairs [k3][32]: dh2 = dOut W3 of the single-head / critic path runs on pairs
     int bars, tmem_slot, end;
     int ldo, n3a;                        // logits row stride (floats), padded actor logit count
 };
@@ -74,6 +75,8 @@ __host__ __device__ constexpr TcLayout tc_layout(int K, int np) {
     L.b2_1 = o; o += TC_H * 4;
     L.w3_1 = o; o += TC_H * 4;
     L.b3p_1 = o; o += 4 * 4;
+    L.w3h_0 = o; o += K * TC_H * 2;
+    L.w3h_1 = o; o += TC_H * 2;
     o = (o + 127) & ~127;
     L.p1h_0 = o; o += 4 * TC_H * 16;
     L.p1h_1 = o; o += 4 * TC_H * 16;
@@ -471,44 +474,51 @@ __device__ __forceinline__ void tc_compute_wg(const UpdArgs& a, const TcLayout& 
         // ---- P3: dZ2 = (dOut W3) * (1 - h2^2) -> A2 (over h2, once G5 has read it); G2, G3
         {
             uint4 dz[8];
+            if (NET == 1 || FAST) {
+                // dOut has at most three entries per row: dh2 is formed on packed 16-bit pairs (dOut carries the same
+                // 16-bit rounding as the DO tile the tensor core reads for dW3), straight into the derivative
+                const uint4* W3H = reinterpret_cast<const uint4*>(sm + L.w3h(NET));
+                uint32_t g2[KR];
+                if (NET == 1) g2[0] = pack2<FMT>(gvc, gvc);
+                else
 #pragma unroll
-            for (int cc = 0; cc < 8; cc++) {   // 8 hidden units at a time: d = dOut W3[:, 8 cc ..), then the derivative
-                float d[8];
-                if (NET == 1) {
-                    const float4 w0 = *reinterpret_cast<const float4*>(W3 + cc * 8);
-                    const float4 w1 = *reinterpret_cast<const float4*>(W3 + cc * 8 + 4);
-                    d[0] = gvc * w0.x; d[1] = gvc * w0.y; d[2] = gvc * w0.z; d[3] = gvc * w0.w;
-                    d[4] = gvc * w1.x; d[5] = gvc * w1.y; d[6] = gvc * w1.z; d[7] = gvc * w1.w;
-                } else {
+                    for (int q = 0; q < KR; q++) g2[q] = pack2<FMT>(xr[q], xr[q]);
 #pragma unroll
-                    for (int i = 0; i < 8; i++) d[i] = 0.0f;
-                    if (FAST) {
+                for (int cc = 0; cc < 8; cc++) {
+                    uint4 w = W3H[cc];
+                    uint4 d = {hmul2<FMT>(g2[0], w.x), hmul2<FMT>(g2[0], w.y), hmul2<FMT>(g2[0], w.z), hmul2<FMT>(g2[0], w.w)};
+                    if (NET == 0) {
 #pragma unroll
-                        for (int q = 0; q < KR; q++) {
-                            const float4 w0 = *reinterpret_cast<const float4*>(W3 + q * TC_H + cc * 8);
-                            const float4 w1 = *reinterpret_cast<const float4*>(W3 + q * TC_H + cc * 8 + 4);
-                            d[0] = fmaf(xr[q], w0.x, d[0]); d[1] = fmaf(xr[q], w0.y, d[1]);
-                            d[2] = fmaf(xr[q], w0.z, d[2]); d[3] = fmaf(xr[q], w0.w, d[3]);
-                            d[4] = fmaf(xr[q], w1.x, d[4]); d[5] = fmaf(xr[q], w1.y, d[5]);
-                            d[6] = fmaf(xr[q], w1.z, d[6]); d[7] = fmaf(xr[q], w1.w, d[7]);
-                        }
-                    } else {
-                        for (int q = 0; q < K; q++) {
-                            const float dq = x[q];
-                            const float4 w0 = *reinterpret_cast<const float4*>(W3 + q * TC_H + cc * 8);
-                            const float4 w1 = *reinterpret_cast<const float4*>(W3 + q * TC_H + cc * 8 + 4);
-                            d[0] = fmaf(dq, w0.x, d[0]); d[1] = fmaf(dq, w0.y, d[1]);
-                            d[2] = fmaf(dq, w0.z, d[2]); d[3] = fmaf(dq, w0.w, d[3]);
-                            d[4] = fmaf(dq, w1.x, d[4]); d[5] = fmaf(dq, w1.y, d[5]);
-                            d[6] = fmaf(dq, w1.z, d[6]); d[7] = fmaf(dq, w1.w, d[7]);
+                        for (int q = 1; q < KR; q++) {
+                            w = W3H[q * 8 + cc];
+                            d.x = hfma2<FMT>(g2[q], w.x, d.x); d.y = hfma2<FMT>(g2[q], w.y, d.y);
+                            d.z = hfma2<FMT>(g2[q], w.z, d.z); d.w = hfma2<FMT>(g2[q], w.w, d.w);
                         }
                     }
+                    // h2 comes back from its 16-bit copy (this thread wrote it in P2)
+                    const uint4 hq = *reinterpret_cast<const uint4*>(A2 + act_chunk_off(wt, cc));
+                    dz[cc].x = dtanh2p<FMT>(d.x, hq.x); dz[cc].y = dtanh2p<FMT>(d.y, hq.y);
+                    dz[cc].z = dtanh2p<FMT>(d.z, hq.z); dz[cc].w = dtanh2p<FMT>(d.w, hq.w);
                 }
-                // h2 comes back from its 16-bit copy (this thread wrote it in P2); the derivative factor and the product
-                // are formed on packed pairs (umma.cuh: dtanh2)
-                const uint4 hq = *reinterpret_cast<const uint4*>(A2 + act_chunk_off(wt, cc));
-                dz[cc].x = dtanh2<FMT>(d[0], d[1], hq.x); dz[cc].y = dtanh2<FMT>(d[2], d[3], hq.y);
-                dz[cc].z = dtanh2<FMT>(d[4], d[5], hq.z); dz[cc].w = dtanh2<FMT>(d[6], d[7], hq.w);
+            } else {
+#pragma unroll
+                for (int cc = 0; cc < 8; cc++) {   // 8 hidden units at a time: d = dOut W3[:, 8 cc ..), then the derivative
+                    float d[8];
+#pragma unroll
+                    for (int i = 0; i < 8; i++) d[i] = 0.0f;
+                    for (int q = 0; q < K; q++) {
+                        const float dq = x[q];
+                        const float4 w0 = *reinterpret_cast<const float4*>(W3 + q * TC_H + cc * 8);
+                        const float4 w1 = *reinterpret_cast<const float4*>(W3 + q * TC_H + cc * 8 + 4);
+                        d[0] = fmaf(dq, w0.x, d[0]); d[1] = fmaf(dq, w0.y, d[1]);
+                        d[2] = fmaf(dq, w0.z, d[2]); d[3] = fmaf(dq, w0.w, d[3]);
+                        d[4] = fmaf(dq, w1.x, d[4]); d[5] = fmaf(dq, w1.y, d[5]);
+                        d[6] = fmaf(dq, w1.z, d[6]); d[7] = fmaf(dq, w1.w, d[7]);
+                    }
+                    const uint4 hq = *reinterpret_cast<const uint4*>(A2 + act_chunk_off(wt, cc));
+                    dz[cc].x = dtanh2<FMT>(d[0], d[1], hq.x); dz[cc].y = dtanh2<FMT>(d[2], d[3], hq.y);
+                    dz[cc].z = dtanh2<FMT>(d[4], d[5], hq.z); dz[cc].w = dtanh2<FMT>(d[6], d[7], hq.w);
+                }
             }
             TC_TS(tsb + 5);
             mbar_wait(doneW, pw); pw ^= 1u;  // G5 has read A2 / DO
@@ -633,6 +643,11 @@ __global__ void __launch_bounds__((2 * NP + 1) * 128, 1) update_tc_kernel(const 
             }
             *dst = __ldg(src);
         }
+    }
+    for (int e = tid; e < (K + 1) * 32; e += nthreads) {   // W3 as packed pairs, actor rows 0 .. K-1 then the critic's row
+        const int q = e >> 5, j2 = e & 31, net = q < K ? 0 : 1;
+        const float* src = a.params + offs[net].W3 + (net ? 0 : q * TC_H) + 2 * j2;
+        reinterpret_cast<uint32_t*>(sm + L.w3h(net))[(net ? 0 : q * 32) + j2] = pack2<FMT>(__ldg(src), __ldg(src + 1));
     }
     {   // 16-bit layer-1 weights P1[j] = {W1[j][0..O), b1[j], 0..}, K-major no-swizzle chunks {hi, hi, lo, 0}: with the
         // input split the same way (x = hi + lo) two K = 16 MMAs give x.hi P.hi + x.lo P.hi + x.hi P.lo, i.e. layer 1 to
