@@ -387,8 +387,17 @@ def time_trainer(torch, dist, tr, K, W, flush, it0_total):
     return max_over_ranks(ms_dev), max_over_ranks(ms_e2e), wall_dev
 
 
-UPDATE_PATHS = {0: "fp32 FMA kernels (update_kernel)", 1: "tcgen05, hidden = 64, one fused kernel (update_tc_kernel)",
+UPDATE_PATHS = {0: "fp32 FMA kernels (update_kernel)",
+                1: "tcgen05, hidden = 64, one fused kernel (update_tc_kernel: one net per compute warpgroup, 16 compute warps per SM)",
                 2: "tcgen05, hidden = 256: update_h256_kernel (forward + loss + dX, one net per CTA) + dw2_h256_kernel (TMA-fed dW2 GEMM)"}
+
+
+# what actually bounds the update kernel of each path (the dense-bf16 peak is the contract's denominator)
+UPDATE_LIMITER = {
+    1: "shared-memory bandwidth, not the tensor pipe: 64-wide layers make every SS-mode tcgen05.mma cost its operand bytes / "
+       "128 B per clock (profiles/r02d_umma_conc.txt: M128N64K16 48 cycles for 32 cycles of math, M64N8K16 23), and the "
+       "activation tiles cross shared memory 4 times per net and row (LSU wavefronts 54 % of peak + operand fetch ~33 %)",
+    2: "tensor pipe / MUFU / issue slots in about equal thirds (update_h256_kernel); dw2_h256_kernel is at the HBM roofline"}
 
 
 def run_b200(args, wl_name):
@@ -451,6 +460,7 @@ def run_b200(args, wl_name):
                 "traffic_source": None if traffic is None else
                 "constant from the committed ncu --set full capture named beside NCU_TRAFFIC in bench.py, not re-measured by this run",
                 "peak_source": pk["source"] + " (bf16 cuBLAS sustained)",
+                "limiter": UPDATE_LIMITER.get(path),
                 "flops_per_launch": flops_per_launch, "rows_per_launch": mb_rows, "ms_per_launch": upd_ms_per,
                 "share_of_step": upd_ms / phase_total if phase_total else None}
     # one GPU / peer-memory DP: scalars, rollout, gae, all-epoch advantage statistics, row packing, per minibatch {update,
