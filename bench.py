@@ -41,7 +41,13 @@ REF_SAMPLE_ENVS = 32768   # env count the CPU arm runs when the workload itself 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE update-kernel launch from an `ncu --set full` capture of this
 # command (profiles/r01r_update_tc_ncu.txt, cold L2): 14.82 MB.  Algorithmic bytes per launch are 131072 rows x
 # 36 B = 4.7 MB, fetched as 64-byte packed records = 8.4 MB (ppo_pack_rows), + 37 KB of parameters per CTA.
-NCU_TRAFFIC = {("cartpole_4096x128_h64", 2): 14.82e6,
+NCU_TRAFFIC = {("cartpole_4096x128_h64", 2): 14.82e6,   # (capture of the round-1 kernel)
+               # north-star shape on one GPU, 33.5 M rows per launch (profiles/r02f_update_tc_default_ncu.txt): 8.14 GB read + 11 MB
+               # written = 243 B per row.  Algorithmic: 36 B per row, fetched as a 64-byte packed record by BOTH warpgroups of a
+               # tile stream (actor and critic each read the row; free-running they drift ~15 tiles apart, so the second read
+               # misses L2).  Keeping the critic within 1-3 tiles of the actor halves this to 4.28 GB (measured) but costs 1.5-1.8 %
+               # of the step (A/B on one box), and DRAM is at 16 % of its peak here: not done.
+               ("cartpole_1048576x128_h64", 2): 8.154e9,
                # hidden = 256 (profiles/r02a_update_h256_ncu.txt): update_h256_kernel 1.04 GB read + 8.55 GB written (the fp16 h1 /
                # dZ2 scratch of 4.19 M rows x 2 nets), dw2_h256_kernel 8.60 GB read + 0.07 GB written
                ("mountaincar_65536x256_h256", 2): 18.25e9}
@@ -452,7 +458,7 @@ def run_b200(args, wl_name):
     phase_total = sum(v[0] for v in phases.values())
     mode = P.ops.get_math_mode()
     path = int(P.capi.load().ppo_update_path(C.byref(tr.cfg.dims)))     # which kernels serve this shape in this mode
-    traffic = NCU_TRAFFIC.get((wl_name, mode))
+    traffic = NCU_TRAFFIC.get((wl_name, mode)) if (world == 1 or not total) else None   # per-launch captures are per shard size
     roofline = {"bound": "tensor", "kernel": "fused fwd + PPO loss + bwd of one minibatch: " + UPDATE_PATHS.get(path, "?"),
                 "achieved": achieved_tf, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
                 "frac": achieved_tf / pk["bf16_sustained"],
