@@ -126,6 +126,13 @@ __global__ void __launch_bounds__(STAT_THREADS) adv_stats_kernel(const float* __
 // finish (ticket) sums the slices in fixed order and writes the statistics.  workspace = [n_mb][ADV_SLICES][2] doubles
 // + [n_mb] uint32 tickets, zeroed once by the caller and left zeroed.
 constexpr int ADV_SLICES = 32, ADV_THREADS = 256;
+// Workspace layout shared by the three sliced kernels below (a trainer hands the same buffer to all of them): a fixed
+// header of ADV_TICKETS uint32 arrival tickets, then the double partials.  (Until round 2 every kernel put its tickets
+// BEHIND its own partials, i.e. inside another kernel's partials: after an all-epoch launch the per-epoch kernel found
+// garbage tickets, never elected a last CTA and left the statistics of the previous launch in place.)
+constexpr int ADV_TICKETS = 1024;
+__device__ __forceinline__ unsigned int* adv_tickets(double* ws) { return reinterpret_cast<unsigned int*>(ws); }
+__device__ __forceinline__ double* adv_partials(double* ws) { return ws + ADV_TICKETS / 2; }
 __global__ void __launch_bounds__(ADV_THREADS) adv_moments_kernel(const float* __restrict__ adv,
                                                                   const int32_t* __restrict__ perm, int64_t batch,
                                                                   int mb_size, int n_mb, double* __restrict__ ws,
@@ -149,7 +156,8 @@ __global__ void __launch_bounds__(ADV_THREADS) adv_moments_kernel(const float* _
     }
     s = block_sum<ADV_THREADS>(s, sh);
     q = block_sum<ADV_THREADS>(q, sh);
-    unsigned int* tickets = reinterpret_cast<unsigned int*>(ws + (size_t)n_mb * ADV_SLICES * 2);
+    unsigned int* tickets = adv_tickets(ws);
+    ws = adv_partials(ws);
     if (threadIdx.x == 0) {
         ws[((size_t)mb * ADV_SLICES + sl) * 2 + 0] = s;
         ws[((size_t)mb * ADV_SLICES + sl) * 2 + 1] = q;
@@ -291,8 +299,8 @@ __global__ void __launch_bounds__(ADV_THREADS) adv_moments_all_kernel(const floa
     }
     s = block_sum<ADV_THREADS>(s, sh);
     q = block_sum<ADV_THREADS>(q, sh);
-    const int n_all = n_epochs * n_mb;
-    unsigned int* tickets = reinterpret_cast<unsigned int*>(ws + (size_t)n_all * ADV_SLICES * 2);
+    unsigned int* tickets = adv_tickets(ws);
+    ws = adv_partials(ws);
     if (threadIdx.x == 0) {
         ws[((size_t)emb * ADV_SLICES + sl) * 2 + 0] = s;
         ws[((size_t)emb * ADV_SLICES + sl) * 2 + 1] = q;
@@ -329,6 +337,7 @@ __global__ void __launch_bounds__(ADV_THREADS) adv_moments_all_kernel(const floa
 // here.  Grid (epoch, chunk): a CTA sums its chunk's rows into per-minibatch registers (double), ws[e][mb][chunk]; the
 // last CTA of an epoch adds the chunks in fixed order => run-to-run identical.
 constexpr int ADV_MBMAX = 8;
+constexpr int ADV_CSLICES_MAX = 128;   // slices per epoch of the coalesced kernel (grid.y, chosen at launch): workspace bound
 __global__ void __launch_bounds__(ADV_THREADS) adv_moments_all_coalesced_kernel(
     const float* __restrict__ adv, int64_t batch, int mb_size, int n_mb, int n_epochs, int half_bits, uint64_t seed,
     uint64_t epoch0, const uint64_t* __restrict__ d_epoch, double* __restrict__ ws, float* __restrict__ stats_out,
@@ -338,7 +347,8 @@ __global__ void __launch_bounds__(ADV_THREADS) adv_moments_all_coalesced_kernel(
     const int e = blockIdx.x, c = blockIdx.y;
     uint32_t key[4];
     perm_keys(seed, epoch0 + (uint64_t)e + (d_epoch ? *d_epoch : 0ull), key);
-    const int64_t per = (((batch + ADV_SLICES - 1) / ADV_SLICES) + 3) & ~(int64_t)3;
+    const int nsl = (int)gridDim.y;
+    const int64_t per = (((batch + nsl - 1) / nsl) + 3) & ~(int64_t)3;
     const int64_t i0 = c * per, i1 = i0 + per < batch ? i0 + per : batch;
     // fp64 adds issue at ~2 per clock and SM on this part (the first version, 16 predicated double adds per row, ran at
     // 7 clocks per row): rows go into fp32 per-minibatch registers, flushed into the double accumulators every 32 rows
@@ -375,31 +385,31 @@ __global__ void __launch_bounds__(ADV_THREADS) adv_moments_all_coalesced_kernel(
     }
     for (int64_t t = i; t < i1 && t < i + 4; t++) add(__ldg(adv + t), t);   // the ragged tail of the last chunk
     flush();
-    const int n_all = n_epochs * n_mb;
-    unsigned int* tickets = reinterpret_cast<unsigned int*>(ws + (size_t)n_all * ADV_SLICES * 2);
+    unsigned int* tickets = adv_tickets(ws);
+    ws = adv_partials(ws);
 #pragma unroll
     for (int m = 0; m < ADV_MBMAX; m++) {
         if (m < n_mb) {
             const double S = block_sum<ADV_THREADS>(s[m], sh);
             const double Q = block_sum<ADV_THREADS>(q[m], sh);
             if (threadIdx.x == 0) {
-                ws[((size_t)(e * n_mb + m) * ADV_SLICES + c) * 2 + 0] = S;
-                ws[((size_t)(e * n_mb + m) * ADV_SLICES + c) * 2 + 1] = Q;
+                ws[((size_t)(e * n_mb + m) * nsl + c) * 2 + 0] = S;
+                ws[((size_t)(e * n_mb + m) * nsl + c) * 2 + 1] = Q;
             }
         }
     }
     if (threadIdx.x == 0) {
         __threadfence();
-        last = (atomicAdd(tickets + e, 1u) == ADV_SLICES - 1);
+        last = (atomicAdd(tickets + e, 1u) == (unsigned)nsl - 1u);
     }
     __syncthreads();
     if (!last || threadIdx.x >= n_mb) return;
     __threadfence();
     const int m = threadIdx.x, emb = e * n_mb + m;
     double S = 0.0, Q = 0.0;
-    for (int k = 0; k < ADV_SLICES; k++) {
-        S += ws[((size_t)emb * ADV_SLICES + k) * 2 + 0];
-        Q += ws[((size_t)emb * ADV_SLICES + k) * 2 + 1];
+    for (int k = 0; k < nsl; k++) {
+        S += ws[((size_t)emb * nsl + k) * 2 + 0];
+        Q += ws[((size_t)emb * nsl + k) * 2 + 1];
     }
     int64_t cnt = batch - (int64_t)m * mb_size;
     if (cnt > mb_size) cnt = mb_size;
@@ -454,7 +464,7 @@ extern "C" int ppo_clip_adamw(float* params, float* grads, float* exp_avg, float
 }
 
 extern "C" int64_t ppo_adv_stats_workspace_bytes(int n_mb) {
-    return n_mb < 0 ? -1 : (int64_t)n_mb * ADV_SLICES * 2 * (int64_t)sizeof(double) + (int64_t)n_mb * 4 + 16;
+    return n_mb < 0 ? -1 : (int64_t)ADV_TICKETS * 4 + (int64_t)n_mb * ADV_CSLICES_MAX * 2 * (int64_t)sizeof(double);
 }
 
 extern "C" int ppo_adv_stats(const float* adv, const int32_t* perm, int64_t batch, int mb_size, int n_mb,
@@ -462,7 +472,7 @@ extern "C" int ppo_adv_stats(const float* adv, const int32_t* perm, int64_t batc
     PPO_REQUIRE(adv && mb_size >= 1 && n_mb >= 0 && batch >= 0, "ppo_adv_stats: bad arguments");
     PPO_REQUIRE(stats_out || partial_out, "ppo_adv_stats: no output requested");
     if (n_mb == 0) return PPO_OK;
-    if (workspace && mb_size >= 4 * ADV_SLICES * ADV_THREADS)
+    if (workspace && mb_size >= 4 * ADV_SLICES * ADV_THREADS && n_mb <= ADV_TICKETS)
         adv_moments_kernel<<<dim3(n_mb, ADV_SLICES), ADV_THREADS, 0, as_stream(stream)>>>(
             adv, perm, batch, mb_size, n_mb, reinterpret_cast<double*>(workspace), stats_out, partial_out);
     else
@@ -681,12 +691,18 @@ extern "C" int ppo_adv_stats_all_epochs(const float* adv, int64_t batch, int mb_
                 "ppo_adv_stats_all_epochs: bad arguments");
     PPO_REQUIRE(stats_out || partial_out, "ppo_adv_stats_all_epochs: no output requested");
     if (n_mb == 0 || n_epochs == 0) return PPO_OK;
+    PPO_REQUIRE((int64_t)n_mb * n_epochs <= ADV_TICKETS, "ppo_adv_stats_all_epochs: more than %d minibatches per update", ADV_TICKETS);
     // one coalesced pass per epoch once the advantages outgrow L2 (the permuted gathers turn into DRAM sectors); rows of
     // a partial minibatch (batch % n_mb != 0) are handled alike: position / mb_size may reach n_mb - 1 only
     // (below ~31 M rows `adv` stays L2-resident and the gathers are cheaper: 0.83 vs 1.05 ms at 16.8 M rows)
     if (n_mb <= ADV_MBMAX && n_epochs <= 1024 && (g_adv_impl == 2 || (g_adv_impl == 1 && batch >= (1 << 25)))) {
         double* ws = reinterpret_cast<double*>(workspace);
-        adv_moments_all_coalesced_kernel<<<dim3(n_epochs, ADV_SLICES), ADV_THREADS, 0, as_stream(stream)>>>(
+        // slices per epoch: 5 CTAs per SM over the whole grid (10 epochs x 32 slices = 320 CTAs left 24 of 148 SMs with three
+        // CTAs and the rest with two: the launch ran at the pace of the three)
+        const int sms = sm_count() > 0 ? sm_count() : 148;
+        int nsl = (5 * sms + n_epochs / 2) / n_epochs;
+        nsl = nsl < 16 ? 16 : (nsl > ADV_CSLICES_MAX ? ADV_CSLICES_MAX : nsl);
+        adv_moments_all_coalesced_kernel<<<dim3(n_epochs, nsl), ADV_THREADS, 0, as_stream(stream)>>>(
             adv, batch, mb_size, n_mb, n_epochs, perm_half_bits(batch), seed, epoch0, d_epoch, ws, stats_out, partial_out);
         PPO_LAUNCH_CHECK();
         return PPO_OK;

@@ -497,6 +497,33 @@ def test_adv_stats_all_epochs_coalesced_equals_gather(P, request, batch, n_mb):
     assert torch.equal(torch.nan_to_num(s1c, nan=-7.0), torch.nan_to_num(s1, nan=-7.0))   # a 1-row minibatch has std NaN
 
 
+def test_adv_stats_kernels_share_one_workspace(P, request):
+    """a trainer hands ONE workspace to the all-epoch kernels (fused iterate) and to the per-epoch sliced kernel (split
+    phases, profiling, NCCL path): each must find the arrival tickets zeroed by whichever ran before it"""
+    lib = P.capi.load()
+    request.addfinalizer(lambda: lib.ppo_debug_adv_impl(1))
+    batch, n_mb, E, seed = 1 << 22, 4, 3, 5
+    mb_size = batch // n_mb
+    rng = np.random.default_rng(4)
+    adv = dev((rng.standard_normal(batch) * 1.5 - 0.2).astype(np.float32))
+    ws = torch.zeros(lib.ppo_adv_stats_workspace_bytes(n_mb * E), dtype=torch.uint8, device="cuda")
+    perm = P.ops.make_permutation(batch, seed, 0)
+    want = []
+    for m in range(n_mb):
+        x = adv[perm[m * mb_size:(m + 1) * mb_size].long()].double()
+        want.append([x.mean().item(), x.std(unbiased=True).item()])
+    for impl in (2, 0, 2):
+        lib.ppo_debug_adv_impl(impl)
+        out_all = torch.zeros((n_mb * E, 2), device="cuda")
+        P.capi.check(lib.ppo_adv_stats_all_epochs(P.capi.ptr(adv), batch, mb_size, n_mb, E, seed, 0, None, P.capi.ptr(out_all),
+                                                  None, P.capi.ptr(ws), P.capi.stream_ptr()))
+        np.testing.assert_allclose(out_all[:n_mb].cpu().numpy(), want, rtol=1e-5)
+        out = torch.full((n_mb, 2), -1.0, device="cuda")        # the per-epoch sliced kernel on the SAME workspace
+        P.capi.check(lib.ppo_adv_stats(P.capi.ptr(adv), P.capi.ptr(perm), batch, mb_size, n_mb, P.capi.ptr(out), None,
+                                       P.capi.ptr(ws), P.capi.stream_ptr()))
+        np.testing.assert_allclose(out.cpu().numpy(), want, rtol=1e-5)
+
+
 # ---------------------------------------------------------------------------------------------- rollout
 @pytest.mark.parametrize("kind,O,nvec,masked,H,n,T", [(0, 4, [2], False, 64, 100, 24), (0, 4, [1], False, 64, 8, 32),
                                                       (1, 2, [3], True, 64, 77, 20), (1, 2, [3], False, 256, 40, 6),
