@@ -34,7 +34,12 @@ WORKLOADS = {
     "cartpole_1048576x128_h64": dict(env=0, O=4, nvec=(2,), H=64, N=1048576, T=128, MB=4, E=10, max_ep=500, total=True),
     "mountaincar_65536x256_h256": dict(env=1, O=2, nvec=(3,), H=256, N=65536, T=256, MB=4, E=10, max_ep=200),
     "cartpole_8x32_h64": dict(env=0, O=4, nvec=(2,), H=64, N=8, T=32, MB=4, E=10, max_ep=500),
+    # BASELINE configs[3] through the trainer: PPO_MultiDiscrete, 8 CategoricalMasked heads (nvec {3,3,3,3,3,2,2,2}), 262 144 envs of
+    # the synthetic MultiWalk environment (state-dependent masks; ppo-libtorch_b200/csrc/env.cuh)
+    "multiwalk_262144x32_h64": dict(env=2, O=4, nvec=(3, 3, 3, 3, 3, 2, 2, 2), H=64, N=262144, T=32, MB=4, E=10, max_ep=50,
+                                    masked=True),
 }
+ENV_NAMES = {0: "CartPole", 1: "MountainCar", 2: "MultiWalk (synthetic, masked MultiDiscrete)"}
 DEFAULT_WORKLOAD = "cartpole_1048576x128_h64"
 CONFIG_B = "cartpole_4096x128_h64"
 REF_SAMPLE_ENVS = 32768   # env count the CPU arm runs when the workload itself would take hours on host cores
@@ -150,6 +155,9 @@ def run_reference(args, wl_name):
         ref_envs = REF_SAMPLE_ENVS
         wl["N"] = ref_envs
         base["config"]["reference_sample_envs"] = ref_envs
+    if wl["env"] == 2:
+        print(json.dumps(dict(base, unavailable="MultiWalk is a synthetic environment of this repo: the reference has no CPU implementation of it")))
+        return 0
     if not os.path.exists(binary):
         print(json.dumps(dict(base, unavailable="oracle/_ref/ppo_ref not built (needs /root/reference at build time)")))
         return 0
@@ -334,7 +342,8 @@ def make_trainer(P, torch, dist, wl, n_local, rank, world, args):
     """one trainer per rank on its env shard; N>1: NCCL communicator (advantage moments) + peer-memory gradient exchange"""
     tr = P.Trainer(env_kind=wl["env"], obs_dim=wl["O"], hidden=wl["H"], nvec=wl["nvec"], num_envs=n_local,
                    num_steps=wl["T"], num_minibatches=wl["MB"], update_epochs=wl["E"], max_episode_steps=wl["max_ep"],
-                   seed=2, world_size=world, rank=rank, use_cuda_graph=not args.no_graph, **HYPER)
+                   seed=2, world_size=world, rank=rank, use_cuda_graph=not args.no_graph, masked=bool(wl.get("masked")),
+                   **HYPER)
     exchange = "none"
     if world > 1:
         uid = [P.unique_id() if rank == 0 else None]
@@ -483,7 +492,7 @@ def run_b200(args, wl_name):
             "warmup": W, "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "strong" if total else "weak",
             "vs_baseline": None,
             "dtype": {0: "f32", 1: "bf16", 2: "f16"}[mode], "data": "synthetic",
-            "config": {"workload": wl_name, "env": "CartPole" if wl["env"] == 0 else "MountainCar",
+            "config": {"workload": wl_name, "env": ENV_NAMES[wl["env"]],
                        "envs_total": n_local * world, "envs_per_gpu": n_local, "rollout_steps": wl["T"],
                        "hidden": wl["H"], "update_epochs": wl["E"],
                        "minibatches": wl["MB"], "global_batch": batch * world, "parallelism": f"dp{world}",
