@@ -146,6 +146,92 @@ __device__ inline void actor_row_loss_fast1(float* x, int K, int aa, float old_l
 }
 
 
+// actor_row_loss for the tensor-core path (any head layout, optional mask) with the fast intrinsics: the forward values
+// carry ~1e-3 relative error from the 16-bit operands already.  One exponential per logit and pass, no IEEE division, and
+// no per-head arrays (runtime-indexed arrays live in local memory): pass 1 overwrites every logit with its log-prob
+// (-inf marks a masked one), pass 2 turns the log-probs into dL/dlogits.  Same formulas as actor_row_loss.
+// apack (heads <= 8): the row's actions as 8-bit fields, prefetched with the row; else they are read through `act`.
+__device__ inline void actor_row_loss_fast_multi(float* x, const Dims& d, bool masked, uint64_t mbits, const int32_t* act,
+                                                 uint64_t apack, float old_logp, float adv_raw, const ppo_hyper& hp,
+                                                 float meanf, float rstd, RowSumsF& s) {
+    const bool packed_act = d.heads <= 8;
+    auto action_of = [&](int h) { return packed_act ? (int)((apack >> (8 * h)) & 0xFFull) : act[h]; };
+    const int heads = d.heads;
+    const float c = hp.clip_coef, lo = 1.0f - c, hi = 1.0f + c;
+    const bool exact = masked || hp.entropy_mode == PPO_ENTROPY_EXACT;
+    const uint32_t mlo = (uint32_t)mbits, mhi = (uint32_t)(mbits >> 32);
+    auto valid_at = [&](int g) { return !masked || (((g < 32 ? mlo : mhi) >> (g & 31)) & 1u); };
+    float newlogp = 0.0f, ent = 0.0f;
+    int off = 0;
+    for (int h = 0; h < heads; h++) {
+        const int Kh = d.nvec[h];
+        float mx = -INFINITY;
+        for (int j = 0; j < Kh; j++)
+            if (valid_at(off + j)) mx = fmaxf(mx, x[off + j]);
+        float sum = 0.0f;
+        for (int j = 0; j < Kh; j++)
+            if (valid_at(off + j)) sum += __expf(x[off + j] - mx);
+        const float lse = mx + __logf(sum);
+        float eh = 0.0f;
+        for (int j = 0; j < Kh; j++) {
+            const bool v = valid_at(off + j);
+            const float lp = v ? x[off + j] - lse : -INFINITY;
+            x[off + j] = lp;
+            if (exact && v) {
+                const float p = __expf(lp);
+                if (p > 0.0f) eh -= lp * p;
+            }
+        }
+        const float lpa = x[off + action_of(h)];
+        newlogp += lpa == -INFINITY ? -1e8f - lse : lpa;   // CategoricalMasked.cpp:35: a masked logit reads -1e8
+        ent += exact ? eh : -FLT_MIN;                        // Categorical.cpp:114-117
+        off += Kh;
+    }
+    const float logratio = newlogp - old_logp;
+    const float ratio = __expf(logratio);
+    s.kl += (ratio - 1.0f) - logratio;
+    if (fabsf(ratio - 1.0f) > c) s.clip += 1.0f;
+    float A = adv_raw;
+    if (hp.norm_adv) A = (A - meanf) * rstd;
+    const float rc = ratio < lo ? lo : (ratio > hi ? hi : ratio);
+    const float pg1 = -A * ratio, pg2 = -A * rc;
+    s.pg += pg1 > pg2 ? pg1 : pg2;
+    s.ent += ent;
+    float dpg_dr;
+    if (ratio >= lo && ratio <= hi) dpg_dr = -A;
+    else if (pg1 > pg2) dpg_dr = -A;
+    else if (pg1 == pg2) dpg_dr = -0.5f * A;
+    else dpg_dr = 0.0f;
+    const float g_logp = dpg_dr * ratio;
+    const float ge = hp.ent_coef;
+    const bool ent_grad = exact && ge != 0.0f;
+    off = 0;
+    for (int h = 0; h < heads; h++) {
+        const int Kh = d.nvec[h];
+        const int aa = action_of(h);
+        float eh = 0.0f;
+        if (ent_grad)
+            for (int j = 0; j < Kh; j++) {
+                const float lp = x[off + j];
+                if (lp != -INFINITY) {
+                    const float p = __expf(lp);
+                    if (p > 0.0f) eh -= lp * p;
+                }
+            }
+        for (int j = 0; j < Kh; j++) {
+            const float lp = x[off + j];
+            float dz = 0.0f;
+            if (lp != -INFINITY) {
+                const float p = __expf(lp);
+                dz = g_logp * ((j == aa ? 1.0f : 0.0f) - p);
+                if (ent_grad && p > 0.0f) dz += ge * p * (lp + eh);
+            }
+            x[off + j] = dz;
+        }
+        off += Kh;
+    }
+}
+
 // actor_row_loss_fast1 with the row held in registers (KMAX = compile-time bound of K, loops fully unrolled and predicated):
 // one exponential per logit, reused for the probabilities of the backward pass; no shared-memory round trips inside the
 // dependent chain.  x[0..K) = logits on entry, dL/dlogits on exit.  Same formulas and the same intrinsics.

@@ -225,6 +225,8 @@ struct TcRowIn {
     float o[4];      // obs (O <= 4: prefetched; wider observations are loaded at use)
     float f0, f1;    // actor: old_logp, adv;  critic: ret, old_val
     int act0;        // action of head 0 (single-head fast path)
+    uint64_t mbits;  // generic actor path: the row's mask as bits and (heads <= 8) its actions as 8-bit fields, so that the
+    uint64_t apack;  // loss does not wait for global loads in the middle of P2
     bool on;
 };
 
@@ -279,11 +281,18 @@ __device__ __forceinline__ void tc_compute_wg(const UpdArgs& a, const TcLayout& 
         in.o[0] = in.o[1] = in.o[2] = in.o[3] = 0.0f;
         in.f0 = in.f1 = 0.0f;
         in.act0 = 0;
+        in.mbits = ~0ull;
+        in.apack = 0ull;
         if (in.on) {
             const int64_t r = a.perm ? (int64_t)__ldg(a.perm + a.mb_start + rloc)
                                      : (a.pf.inline_on ? perm_index(a.mb_start + rloc, a.pf.batch, a.pf.half_bits, pkey)
                                                        : a.mb_start + rloc);
             in.r = r;
+            if (NET == 0 && !FAST) {
+                if (masked) in.mbits = pack_mask(a.mask + r * K, K);
+                if (heads <= 8)
+                    for (int h = 0; h < heads; h++) in.apack |= (uint64_t)(__ldg(a.actions + r * heads + h) & 0xFF) << (8 * h);
+            }
             if (a.rec) {   // packed row: {obs[4]} {old_logp, adv, ret, old_val} {action, -, -, -} {-}
                 const float4 q0 = __ldg(a.rec + r * 4);
                 in.o[0] = q0.x; in.o[1] = q0.y; in.o[2] = q0.z; in.o[3] = q0.w;
@@ -421,9 +430,23 @@ __device__ __forceinline__ void tc_compute_wg(const UpdArgs& a, const TcLayout& 
 #pragma unroll
                 for (int q = 0; q < KR; q++) xr[q] += out_half(q);
             } else {
-                for (int q = 0; q < K; q++) {
-                    const float part = out_half(q);
-                    x[q] = (hlf ? x[q] : B3[q]) + part;
+                // four output units at a time: 8 independent accumulation chains instead of 2 (the 21-logit MultiDiscrete
+                // shape spent its P2 in the latency of 16-deep FFMA chains)
+                for (int q0 = 0; q0 < K; q0 += 4) {
+                    float a0[4] = {0.f, 0.f, 0.f, 0.f}, a1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int cc = 0; cc < 8; cc++) {
+#pragma unroll
+                        for (int u = 0; u < 4; u++) {
+                            const int q = q0 + u < K ? q0 + u : K - 1;   // the tail repeats the last unit (discarded below)
+                            const float4 w = *reinterpret_cast<const float4*>(W3 + q * TC_H + hlf * 32 + cc * 4);
+                            a0[u] = fmaf(h2[cc * 4 + 0], w.x, a0[u]); a1[u] = fmaf(h2[cc * 4 + 1], w.y, a1[u]);
+                            a0[u] = fmaf(h2[cc * 4 + 2], w.z, a0[u]); a1[u] = fmaf(h2[cc * 4 + 3], w.w, a1[u]);
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        if (q0 + u < K) x[q0 + u] = (hlf ? x[q0 + u] : B3[q0 + u]) + (a0[u] + a1[u]);
                 }
             }
         }
@@ -449,8 +472,8 @@ __device__ __forceinline__ void tc_compute_wg(const UpdArgs& a, const TcLayout& 
             store8<FMT>(DO + wt * 16, v);
         } else {
             if (on) {
-                const uint64_t mbits = masked ? pack_mask(a.mask + cur.r * K, K) : ~0ull;
-                actor_row_loss(x, a.d, masked, mbits, a.actions + cur.r * heads, cur.f0, cur.f1, a.hp, meanf, stdf, 1.0f, rs);
+                actor_row_loss_fast_multi(x, a.d, masked, cur.mbits, a.actions + cur.r * heads, cur.apack, cur.f0, cur.f1, a.hp, meanf,
+                                          rstd, rs);
                 for (int q = 0; q < K; q++) b3acc[q] += x[q];
             } else {
                 for (int q = 0; q < K; q++) x[q] = 0.0f;
