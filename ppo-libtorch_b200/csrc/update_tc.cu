@@ -53,9 +53,15 @@ struct TcLayout {   // byte offsets into the 1024-aligned dynamic shared memory
     TC_PAIR(w3h)     // W3 as packed 16-bit pairs [k3][32]: dh2 = dOut W3 of the single-head / critic path runs on pairs
     int bars, tmem_slot, end;
     int ldo, n3a;                        // logits row stride (floats), padded actor logit count
+    // generic head path (KT = 0): the actor's output layer and dh2 = dOut W3 run on the tensor core
+    int w3k;         // W3 as two 16-bit K-major swizzled tiles [32 units][64] (hi, lo at + 4096): B of the logits MMA (G7)
+    int w3t;         // W3^T [64 hidden][32 units] 16-bit K-major narrow chunks: B of the dh2 MMA (G6)
+    int n7, kq;      // N of G7 (K rounded up to 16), K-steps of G6 (n3a rounded up to 16, / 16)
 };
+// tensor-memory columns of the logits accumulator of stream g (generic path), behind the gradient accumulators
+__host__ __device__ constexpr int tc_lgcol(int np, int g, int n3a) { return np * 128 + np * (80 + n3a) + g * 32; }
 #undef TC_PAIR
-__host__ __device__ constexpr TcLayout tc_layout(int K, int np) {
+__host__ __device__ constexpr TcLayout tc_layout(int K, int np, bool gen = false) {
     TcLayout L{};
     L.ldo = K | 1;
     L.n3a = (K + 7) & ~7;
@@ -64,7 +70,9 @@ __host__ __device__ constexpr TcLayout tc_layout(int K, int np) {
     L.a1 = 0; L.a2 = ACT_BYTES;
     L.xe_0 = 2 * ACT_BYTES; L.xe_1 = L.xe_0 + 2 * TC_ROWS * 16;
     L.dout = L.xe_1 + 2 * TC_ROWS * 16;
-    L.lg = L.dout + (L.n3a / 8) * TC_ROWS * 16;
+    L.n7 = (K + 15) & ~15;
+    L.kq = (L.n3a + 15) / 16;
+    L.lg = L.dout + (gen ? 2 * L.kq : L.n3a / 8) * TC_ROWS * 16;   // generic: the dOut tile is padded to whole K = 16 steps
     L.b3 = L.lg + ((TC_ROWS * L.ldo * 4 + 15) & ~15);
     L.wg_stride = (L.b3 + ((TC_ROWS * L.ldo * 4 + 15) & ~15) + 1023) & ~1023;
     L.wg0 = 16384;
@@ -80,6 +88,12 @@ __host__ __device__ constexpr TcLayout tc_layout(int K, int np) {
     o = (o + 127) & ~127;
     L.p1h_0 = o; o += 4 * TC_H * 16;
     L.p1h_1 = o; o += 4 * TC_H * 16;
+    L.w3k = 0; L.w3t = 0;
+    if (gen) {
+        o = (o + 1023) & ~1023;
+        L.w3k = o; o += 2 * 32 * 128;
+        L.w3t = o; o += 4 * TC_H * 16;
+    }
     L.bars = o; o += 4 * 3 * 8;          // per compute warpgroup c: doneZ, doneW at [2 c + {0, 1}], ready at [2 NC + c]
     L.tmem_slot = o; o += 16;
     L.end = o;
@@ -136,7 +150,7 @@ struct WgIssue {
 // ST 0..3 = G1, G5, G2+G3, G4 (see the header); ST 4 = G0 alone: Z = XE[par] P1h^T (layer-1 pre-activations, K = 16:
 // the 8 real inputs {obs, 1, 0..} + a zero chunk).  g0_next (ST 3 only): also issue G0 of the NEXT tile (XE[par ^ 1])
 // in front of G4 - Z has just been read by P4 and is free.
-template <int FMT, int NP, int ST>
+template <int FMT, int NP, int ST, bool GEN = false>
 __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int par_, uint64_t* doneZ, uint64_t* doneW,
                                             bool g0_next = false) {
     constexpr uint32_t id_fwd = idesc_f16(FMT, 128, 64, 0, 0);   // Z = A1 W2^T
@@ -165,6 +179,12 @@ __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int p
         const uint64_t da = act_desc_mnmajor(A2, 0), db = narrow_desc_mnmajor(wb + L.dout, TC_ROWS, 0);
         const uint32_t id = net == 0 ? idesc_f16(FMT, 64, L.n3a, 1, 1) : id_n8;
         if (lead) {
+            if (GEN && net == 0) {   // G6: Z = dOut W3 (A = the dOut tile read K-major, B = W3^T), K = 16 kq
+                for (int ks = 0; ks < L.kq; ks++)
+                    mma_f16(Z, narrow_desc_kmajor(wb + L.dout + ks * 2 * (TC_ROWS * 16), TC_ROWS * 16),
+                            narrow_desc_kmajor(sb + L.w3t + ks * 2 * (TC_H * 16), TC_H * 16), id_fwd, ks > 0);
+                mma_commit(doneZ);
+            }
 #pragma unroll
             for (int ks = 0; ks < 8; ks++) mma_f16(tmem + c.w3, da + 128u * ks, db + 16u * ks, id, ks > 0 ? 1u : acc0);
             mma_commit(doneW);
@@ -187,6 +207,18 @@ __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int p
             mma_commit(doneW);
         }
         w.fresh &= ~3u;
+    } else if (ST == 5) {   // G7 (generic actor path): logits = A2 W3^T, W3 as hi + lo so that only h2 carries a 16-bit rounding
+        const uint32_t LG = tmem + (uint32_t)tc_lgcol(NP, g, L.n3a);
+        const uint64_t da = act_desc_kmajor(A2, 0);
+        const uint64_t dbh = act_desc_kmajor(sb + L.w3k, 0), dbl = act_desc_kmajor(sb + L.w3k + 4096, 0);
+        const uint32_t id7 = idesc_f16(FMT, 128, L.n7, 0, 0);
+        if (lead) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) mma_f16(LG, da + 2u * ks, dbh + 2u * ks, id7, ks > 0);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) mma_f16(LG, da + 2u * ks, dbl + 2u * ks, id7, 1u);
+            mma_commit(doneZ);
+        }
     } else if (ST == 4) {
         const uint64_t da = narrow_desc_kmajor(wb + L.xe(par), TC_ROWS * 16);          // {x.hi, x.lo}
         const uint64_t db = narrow_desc_kmajor(sb + L.p1h(net), TC_H * 16);             // {P.hi, P.hi}
@@ -429,25 +461,23 @@ __device__ __forceinline__ void tc_compute_wg(const UpdArgs& a, const TcLayout& 
             } else if (FAST) {
 #pragma unroll
                 for (int q = 0; q < KR; q++) xr[q] += out_half(q);
-            } else {
-                // four output units at a time: 8 independent accumulation chains instead of 2 (the 21-logit MultiDiscrete
-                // shape spent its P2 in the latency of 16-deep FFMA chains)
-                for (int q0 = 0; q0 < K; q0 += 4) {
-                    float a0[4] = {0.f, 0.f, 0.f, 0.f}, a1[4] = {0.f, 0.f, 0.f, 0.f};
+            }
+            // generic actor path: no per-row output layer here - the logits come from the tensor core (G7, below)
+        }
+        if (NET == 0 && !FAST) {
+            tc_fence_before();
+            fence_async_smem();
+            mbar_arrive(ready);          // h2 is staged: G7 = logits
+            mbar_wait(doneZ, pz); pz ^= 1u;
+            tc_fence_after();
+            const uint32_t lgaddr = tmem_addr(tmem, (uint32_t)w4 * 32u, (uint32_t)tc_lgcol(NP, g, L.n3a));
+            for (int c16 = 0; c16 < L.n7 / 16; c16++) {
+                float lg[16];
+                tmem_ld16(lgaddr + c16 * 16, lg);
+                tmem_ld_wait();
 #pragma unroll
-                    for (int cc = 0; cc < 8; cc++) {
-#pragma unroll
-                        for (int u = 0; u < 4; u++) {
-                            const int q = q0 + u < K ? q0 + u : K - 1;   // the tail repeats the last unit (discarded below)
-                            const float4 w = *reinterpret_cast<const float4*>(W3 + q * TC_H + hlf * 32 + cc * 4);
-                            a0[u] = fmaf(h2[cc * 4 + 0], w.x, a0[u]); a1[u] = fmaf(h2[cc * 4 + 1], w.y, a1[u]);
-                            a0[u] = fmaf(h2[cc * 4 + 2], w.z, a0[u]); a1[u] = fmaf(h2[cc * 4 + 3], w.w, a1[u]);
-                        }
-                    }
-#pragma unroll
-                    for (int u = 0; u < 4; u++)
-                        if (q0 + u < K) x[q0 + u] = (hlf ? x[q0 + u] : B3[q0 + u]) + (a0[u] + a1[u]);
-                }
+                for (int i = 0; i < 16; i++)
+                    if (c16 * 16 + i < K) x[c16 * 16 + i] = lg[i] + B3[c16 * 16 + i];
             }
         }
         if (NET == 1) {
@@ -524,24 +554,23 @@ __device__ __forceinline__ void tc_compute_wg(const UpdArgs& a, const TcLayout& 
                     dz[cc].z = dtanh2p<FMT>(d.z, hq.z); dz[cc].w = dtanh2p<FMT>(d.w, hq.w);
                 }
             } else {
+                // generic actor path: dh2 = dOut W3 comes from the tensor core (G6, issued with G5 behind P2)
+                mbar_wait(doneZ, pz); pz ^= 1u;
+                tc_fence_after();
 #pragma unroll
-                for (int cc = 0; cc < 8; cc++) {   // 8 hidden units at a time: d = dOut W3[:, 8 cc ..), then the derivative
-                    float d[8];
+                for (int qt = 0; qt < 4; qt++) {
+                    float d[16];
+                    tmem_ld16(zaddr + qt * 16, d);
+                    tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 8; i++) d[i] = 0.0f;
-                    for (int q = 0; q < K; q++) {
-                        const float dq = x[q];
-                        const float4 w0 = *reinterpret_cast<const float4*>(W3 + q * TC_H + cc * 8);
-                        const float4 w1 = *reinterpret_cast<const float4*>(W3 + q * TC_H + cc * 8 + 4);
-                        d[0] = fmaf(dq, w0.x, d[0]); d[1] = fmaf(dq, w0.y, d[1]);
-                        d[2] = fmaf(dq, w0.z, d[2]); d[3] = fmaf(dq, w0.w, d[3]);
-                        d[4] = fmaf(dq, w1.x, d[4]); d[5] = fmaf(dq, w1.y, d[5]);
-                        d[6] = fmaf(dq, w1.z, d[6]); d[7] = fmaf(dq, w1.w, d[7]);
+                    for (int cc = 0; cc < 2; cc++) {
+                        const uint4 hq = *reinterpret_cast<const uint4*>(A2 + act_chunk_off(wt, qt * 2 + cc));
+                        uint4& o = dz[qt * 2 + cc];
+                        o.x = dtanh2<FMT>(d[cc * 8 + 0], d[cc * 8 + 1], hq.x); o.y = dtanh2<FMT>(d[cc * 8 + 2], d[cc * 8 + 3], hq.y);
+                        o.z = dtanh2<FMT>(d[cc * 8 + 4], d[cc * 8 + 5], hq.z); o.w = dtanh2<FMT>(d[cc * 8 + 6], d[cc * 8 + 7], hq.w);
                     }
-                    const uint4 hq = *reinterpret_cast<const uint4*>(A2 + act_chunk_off(wt, cc));
-                    dz[cc].x = dtanh2<FMT>(d[0], d[1], hq.x); dz[cc].y = dtanh2<FMT>(d[2], d[3], hq.y);
-                    dz[cc].z = dtanh2<FMT>(d[4], d[5], hq.z); dz[cc].w = dtanh2<FMT>(d[6], d[7], hq.w);
                 }
+                tc_fence_before();
             }
             TC_TS(tsb + 5);
             mbar_wait(doneW, pw); pw ^= 1u;  // G5 has read A2 / DO
@@ -606,7 +635,7 @@ __global__ void __launch_bounds__((2 * NP + 1) * 128, 1) update_tc_kernel(const 
     constexpr int nthreads = (NC + 1) * 128;    // + the MMA-issue warpgroup
     constexpr TcLayout LC = tc_layout(KT > 0 ? KT : 1, NP);
     const int O = a.d.O, K = KT > 0 ? KT : a.d.K;
-    const TcLayout L = KT > 0 ? LC : tc_layout(K, NP);
+    const TcLayout L = KT > 0 ? LC : tc_layout(K, NP, true);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const NetOff offs[2] = {actor_off(O, TC_H, K), critic_off(O, TC_H)};
     uint64_t* bars = reinterpret_cast<uint64_t*>(sm + L.bars);  // [2 c + {doneZ, doneW}], ready at [2 NC + c]
@@ -665,6 +694,35 @@ __global__ void __launch_bounds__((2 * NP + 1) * 128, 1) update_tc_kernel(const 
                 src = a.params + offs[net].b3 + idx;
             }
             *dst = __ldg(src);
+        }
+    }
+    if (KT == 0) {   // generic head path: operands of the logits MMA (G7) and of dh2 = dOut W3 (G6), zero padding of the dOut tiles
+        for (int e = tid; e < 32 * 8; e += nthreads) {
+            const int q = e >> 3, cc = e & 7;
+            float v[8], lo[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = q < K ? __ldg(a.params + offs[0].W3 + q * TC_H + cc * 8 + i) : 0.0f;
+#pragma unroll
+            for (int i = 0; i < 8; i += 2) {
+                const uint32_t ph = pack2<FMT>(v[i], v[i + 1]);
+                lo[i] = v[i] - unpack_lo<FMT>(ph);
+                lo[i + 1] = v[i + 1] - unpack_hi<FMT>(ph);
+            }
+            store8<FMT>(sm + L.w3k + act_chunk_off(q, cc), v);
+            store8<FMT>(sm + L.w3k + 4096 + act_chunk_off(q, cc), lo);
+        }
+        for (int e = tid; e < 4 * TC_H; e += nthreads) {
+            const int cq = e >> 6, n = e & 63;
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = cq * 8 + i < K ? __ldg(a.params + offs[0].W3 + (cq * 8 + i) * TC_H + n) : 0.0f;
+            store8<FMT>(sm + L.w3t + cq * (TC_H * 16) + n * 16, v);
+        }
+        const int pad0 = L.n3a / 8, npad = 2 * L.kq - pad0;   // dOut chunks beyond the real logits: read by G6, never written
+        for (int e = tid; e < NP * npad * TC_ROWS; e += nthreads) {
+            const int g = e / (npad * TC_ROWS), r = e % (npad * TC_ROWS);
+            float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            store8<FMT>(sm + L.wg0 + (2 * g) * L.wg_stride + L.dout + pad0 * (TC_ROWS * 16) + r * 16, z);
         }
     }
     for (int e = tid; e < (K + 1) * 32; e += nthreads) {   // W3 as packed pairs, actor rows 0 .. K-1 then the critic's row
@@ -732,8 +790,12 @@ __global__ void __launch_bounds__((2 * NP + 1) * 128, 1) update_tc_kernel(const 
                 tiles_done++;
                 mbar_wait(ready, pr); pr ^= 1u;
                 issue_stage<FMT, NP, 0>(D, L, par, doneZ, doneW);
+                if (KT == 0 && (c & 1) == 0) {   // generic actor: the output layer's MMA between the two halves of P2
+                    mbar_wait(ready, pr); pr ^= 1u;
+                    issue_stage<FMT, NP, 5, true>(D, L, par, doneZ, doneW);
+                }
                 mbar_wait(ready, pr); pr ^= 1u;
-                issue_stage<FMT, NP, 1>(D, L, par, doneZ, doneW);
+                issue_stage<FMT, NP, 1, KT == 0>(D, L, par, doneZ, doneW);
                 mbar_wait(ready, pr); pr ^= 1u;
                 issue_stage<FMT, NP, 2>(D, L, par, doneZ, doneW);
                 mbar_wait(ready, pr); pr ^= 1u;
@@ -892,7 +954,7 @@ __global__ void __launch_bounds__((2 * NP + 1) * 128, 1) update_tc_kernel(const 
 
 template <int FMT, int NP, int KT>
 static int launch_tc(UpdArgs& a, int* grid_out, cudaStream_t st) {
-    const TcLayout L = tc_layout(a.d.K, NP);
+    const TcLayout L = tc_layout(a.d.K, NP, KT == 0);
     const size_t smem = (size_t)L.end + 1024;
     PPO_REQUIRE(smem <= 227 * 1024, "update_tc: needs %zu B of shared memory", smem);
     static bool attr_done = false;
@@ -924,7 +986,11 @@ extern "C" int ppo_debug_tc_timeline(long long* d_ts, int who) {
     return PPO_OK;
 }
 namespace ppo {
-static bool tc_fits(int K, int np) { return (size_t)tc_layout(K, np).end + 1024 <= 227 * 1024; }
+// generic-path envelope: shared memory, and the tensor-memory columns (Z, gradient accumulators, logits) within 512
+static bool tc_fits(int K, int np) {
+    const TcLayout L = tc_layout(K, np, true);
+    return (size_t)L.end + 1024 <= 227 * 1024 && tc_lgcol(np, np - 1, L.n3a) + 32 <= 512;
+}
 bool update_tc_supported(const Dims& d) { return d.H == TC_H && d.O + 1 <= 8 && d.K <= TC_MAX_K && tc_fits(d.K, 1); }
 int launch_update_tc(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st, const FuseAdam* fuse, float* grads_out,
                      float* diag_out, bool* tail_done) {

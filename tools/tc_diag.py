@@ -13,18 +13,23 @@ import ppo_libtorch_b200 as P  # noqa: E402
 from test_gpu_tensorcore import _make_case, dev  # noqa: E402
 
 orc = oracle.lib()
-O, nvec, n, masked = 4, [2], int(sys.argv[1]) if len(sys.argv) > 1 else 1000, False
+# usage: tc_diag.py [n] [O] [nvec as 3,3,2] [masked 0/1]
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 1000
+O = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+nvec = [int(v) for v in sys.argv[3].split(",")] if len(sys.argv) > 3 else [2]
+masked = bool(int(sys.argv[4])) if len(sys.argv) > 4 else False
 K, H = sum(nvec), 64
-c = _make_case(P, orc, O, nvec, n + 300, masked, seed=1)
+c = _make_case(P, orc, O, nvec, n + 300, masked, seed=n + 2)
 start = 5
 rows = c["perm"][start:start + n]
 dperm = dev(c["perm"])
 stat = P.ops.adv_stats(dev(c["adv"]), n, 1, perm=dperm[start:start + n].contiguous())
 args = (dev(c["params"]), O, 64, nvec, dev(c["obs"]), dev(c["acts"]), dev(c["old_lp"]), dev(c["adv"]),
         dev(c["ret"]), dev(c["old_val"]), start, n)
-kw = dict(perm=dperm, adv_stat=stat, ent_coef=0.01)
+kw = dict(perm=dperm, adv_stat=stat, ent_coef=0.01, mask=None if c["mask"] is None else dev(c["mask"]))
 og, od = orc.minibatch_grads(c["params"], O, 64, np.array(nvec, np.int32), c["obs"][rows], c["acts"][rows],
-                             c["old_lp"][rows], c["adv"][rows], c["ret"][rows], c["old_val"][rows], ent_coef=0.01)
+                             c["old_lp"][rows], c["adv"][rows], c["ret"][rows], c["old_val"][rows], ent_coef=0.01,
+                             mask=None if c["mask"] is None else c["mask"][rows])
 names, sizes = [], []
 for net, k3 in (("critic", 1), ("actor", K)):
     for nm, sz in (("W1", H * O), ("b1", H), ("W2", H * H), ("b2", H), ("W3", k3 * H), ("b3", k3)):
