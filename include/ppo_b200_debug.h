@@ -44,6 +44,9 @@ int ppo_debug_umma_time(int mode, int fmt, const float* A, const float* B, float
  * (0 M128N64 K/K, 1 M64N64 MN/MN, 2 M64N8 MN/narrow, 3 M128N8 MN/narrow, 4 M128N64 K/MN) from their own tiles into their
  * own tensor-memory columns; d_cycles[0] = SM cycles from the first issue to the last completion. */
 int ppo_debug_umma_conc(int shape, int nwarps, int reps, long long* d_cycles, ppo_stream_t stream);
+/* 10 * (tile streams per CTA) + (K as a template parameter, 0 = generic head path) of the update_tc_kernel variant that serves
+ * a shape, -1 outside the tensor-core envelope (host logic only, no device needed). */
+int ppo_debug_update_tc_variant(const ppo_dims* dims, int masked);
 
 /* 1 (default): ppo_categorical runs the warp-cooperative kernel (one (row, head) per lane) whenever every head has at most
  * 8 logits; 0: the row-per-thread kernel (IEEE expf / logf / division per logit) for every shape. */

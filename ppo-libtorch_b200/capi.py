@@ -156,6 +156,7 @@ _PROTOS = {
     "ppo_debug_tc_timeline": (C.c_int, [_P, C.c_int]),
     "ppo_debug_umma_time": (C.c_int, [C.c_int, C.c_int, _P, _P, _P, C.c_int, _P, _P]),
     "ppo_debug_umma_conc": (C.c_int, [C.c_int, C.c_int, C.c_int, _P, _P]),
+    "ppo_debug_update_tc_variant": (C.c_int, [C.POINTER(Dims), C.c_int]),
 }
 EXPORTS = sorted(_PROTOS)
 

@@ -54,8 +54,8 @@ struct TcLayout {   // byte offsets into the 1024-aligned dynamic shared memory
     int bars, tmem_slot, end;
     int ldo, n3a;                        // logits row stride (floats), padded actor logit count
     // generic head path (KT = 0): the actor's output layer and dh2 = dOut W3 run on the tensor core
-    int w3k;         // W3 as two 16-bit K-major swizzled tiles [32 units][64] (hi, lo at + 4096): B of the logits MMA (G7)
-    int w3t;         // W3^T [64 hidden][32 units] 16-bit K-major narrow chunks: B of the dh2 MMA (G6)
+    int w3k;         // W3 as two 16-bit K-major swizzled tiles [n7 units][64] (hi, lo at + n7 * 128): B of the logits MMA (G7)
+    int w3t;         // W3^T [64 hidden][16 kq units] 16-bit K-major narrow chunks: B of the dh2 MMA (G6)
     int n7, kq;      // N of G7 (K rounded up to 16), K-steps of G6 (n3a rounded up to 16, / 16)
 };
 // tensor-memory columns of the logits accumulator of stream g (generic path), behind the gradient accumulators
@@ -91,8 +91,8 @@ __host__ __device__ constexpr TcLayout tc_layout(int K, int np, bool gen = false
     L.w3k = 0; L.w3t = 0;
     if (gen) {
         o = (o + 1023) & ~1023;
-        L.w3k = o; o += 2 * 32 * 128;
-        L.w3t = o; o += 4 * TC_H * 16;
+        L.w3k = o; o += 2 * L.n7 * 128;          // hi tile, lo tile at + n7 * 128 (2 or 4 KB: swizzle-atom aligned)
+        L.w3t = o; o += 2 * L.kq * TC_H * 16;
     }
     L.bars = o; o += 4 * 3 * 8;          // per compute warpgroup c: doneZ, doneW at [2 c + {0, 1}], ready at [2 NC + c]
     L.tmem_slot = o; o += 16;
@@ -210,7 +210,7 @@ __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int p
     } else if (ST == 5) {   // G7 (generic actor path): logits = A2 W3^T, W3 as hi + lo so that only h2 carries a 16-bit rounding
         const uint32_t LG = tmem + (uint32_t)tc_lgcol(NP, g, L.n3a);
         const uint64_t da = act_desc_kmajor(A2, 0);
-        const uint64_t dbh = act_desc_kmajor(sb + L.w3k, 0), dbl = act_desc_kmajor(sb + L.w3k + 4096, 0);
+        const uint64_t dbh = act_desc_kmajor(sb + L.w3k, 0), dbl = act_desc_kmajor(sb + L.w3k + L.n7 * 128, 0);
         const uint32_t id7 = idesc_f16(FMT, 128, L.n7, 0, 0);
         if (lead) {
 #pragma unroll
@@ -697,7 +697,7 @@ __global__ void __launch_bounds__((2 * NP + 1) * 128, 1) update_tc_kernel(const 
         }
     }
     if (KT == 0) {   // generic head path: operands of the logits MMA (G7) and of dh2 = dOut W3 (G6), zero padding of the dOut tiles
-        for (int e = tid; e < 32 * 8; e += nthreads) {
+        for (int e = tid; e < L.n7 * 8; e += nthreads) {
             const int q = e >> 3, cc = e & 7;
             float v[8], lo[8];
 #pragma unroll
@@ -709,9 +709,9 @@ __global__ void __launch_bounds__((2 * NP + 1) * 128, 1) update_tc_kernel(const 
                 lo[i + 1] = v[i + 1] - unpack_hi<FMT>(ph);
             }
             store8<FMT>(sm + L.w3k + act_chunk_off(q, cc), v);
-            store8<FMT>(sm + L.w3k + 4096 + act_chunk_off(q, cc), lo);
+            store8<FMT>(sm + L.w3k + L.n7 * 128 + act_chunk_off(q, cc), lo);
         }
-        for (int e = tid; e < 4 * TC_H; e += nthreads) {
+        for (int e = tid; e < 2 * L.kq * TC_H; e += nthreads) {
             const int cq = e >> 6, n = e & 63;
             float v[8];
 #pragma unroll
@@ -997,24 +997,30 @@ int launch_update_tc(UpdArgs& a, int fmt, int* grid_out, cudaStream_t st, const 
     (void)fuse; (void)grads_out; (void)diag_out;
     if (tail_done) *tail_done = false;   // the reduction + optimiser tail is always the caller's second launch
     if (!update_tc_supported(a.d)) return PPO_ERR_UNSUPPORTED;
-    // two tile streams per CTA (4 compute warpgroups) when their per-row logit scratch fits next to the activation
-    // tiles, else one (2 compute warpgroups: the 21-logit MultiDiscrete shape nvec {3,3,3,3,3,2,2,2})
-    if (!tc_fits(a.d.K, 2)) {
-        if (fmt == FMT_BF16) return launch_tc<FMT_BF16, 1, 0>(a, grid_out, st);
-        return launch_tc<FMT_F16, 1, 0>(a, grid_out, st);
-    }
-    // single unmasked head of 2 or 3 logits (PPO_Discrete on CartPole / MountainCar): K is a template parameter
+    // single unmasked head of 2 or 3 logits (PPO_Discrete on CartPole / MountainCar): K is a template parameter, two tile
+    // streams per CTA (its layout always fits: checked at compile time below)
     const int kt = (a.d.heads == 1 && a.mask == nullptr && (a.d.K == 2 || a.d.K == 3)) ? a.d.K : 0;
-    if (fmt == FMT_BF16) {
-        if (kt == 2) return launch_tc<FMT_BF16, 2, 2>(a, grid_out, st);
-        if (kt == 3) return launch_tc<FMT_BF16, 2, 3>(a, grid_out, st);
-        return launch_tc<FMT_BF16, 2, 0>(a, grid_out, st);
-    }
-    if (kt == 2) return launch_tc<FMT_F16, 2, 2>(a, grid_out, st);
-    if (kt == 3) return launch_tc<FMT_F16, 2, 3>(a, grid_out, st);
-    return launch_tc<FMT_F16, 2, 0>(a, grid_out, st);
+    static_assert(tc_layout(3, 2).end + 1024 <= 227 * 1024, "the single-head layout must fit two tile streams");
+    if (kt == 2) return fmt == FMT_BF16 ? launch_tc<FMT_BF16, 2, 2>(a, grid_out, st) : launch_tc<FMT_F16, 2, 2>(a, grid_out, st);
+    if (kt == 3) return fmt == FMT_BF16 ? launch_tc<FMT_BF16, 2, 3>(a, grid_out, st) : launch_tc<FMT_F16, 2, 3>(a, grid_out, st);
+    // any other head layout: the generic path, with two tile streams per CTA (4 compute warpgroups) when the per-row logit
+    // scratch and the tensor-core operands of the output layer fit next to the activation tiles, else one (the 21-logit
+    // MultiDiscrete shape nvec {3,3,3,3,3,2,2,2})
+    if (tc_fits(a.d.K, 2))
+        return fmt == FMT_BF16 ? launch_tc<FMT_BF16, 2, 0>(a, grid_out, st) : launch_tc<FMT_F16, 2, 0>(a, grid_out, st);
+    return fmt == FMT_BF16 ? launch_tc<FMT_BF16, 1, 0>(a, grid_out, st) : launch_tc<FMT_F16, 1, 0>(a, grid_out, st);
 }
 }  // namespace ppo
+
+// which update_tc_kernel variant serves a shape: 10 * (tile streams per CTA) + (K as a template parameter, 0 = generic head
+// path); -1 when the shape is outside the tensor-core envelope.  Host logic only (tests/test_host_facade.py pins the
+// single-head shapes to the two-stream template: a dispatch slip once sent them to the generic one-stream kernel at half speed).
+extern "C" int ppo_debug_update_tc_variant(const ppo_dims* dims, int masked) {
+    ppo::Dims d;
+    if (ppo::make_dims(dims, &d) != PPO_OK || !ppo::update_tc_supported(d)) return -1;
+    if (d.heads == 1 && !masked && (d.K == 2 || d.K == 3)) return 20 + d.K;
+    return ppo::tc_fits(d.K, 2) ? 20 : 10;
+}
 
 extern "C" int ppo_debug_fuse_tail(int on) {
     ppo::g_fuse_tail = on;

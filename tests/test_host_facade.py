@@ -186,3 +186,19 @@ def test_library_exports_every_declared_symbol():
         except AttributeError:
             missing.append(n)
     assert not missing, f"declared but not exported: {missing}"
+
+
+def test_update_tc_dispatch_by_shape():
+    """single unmasked heads of 2 / 3 logits (CartPole, MountainCar) must get the two-stream kernel with K as a template
+    parameter; the 21-logit MultiDiscrete shape the generic one-stream kernel (host logic of launch_update_tc, no device)"""
+    import ctypes as C
+    import ppo_libtorch_b200 as P
+    lib = P.capi.load()
+
+    def variant(O, H, nvec, masked=False):
+        d = P.capi.Dims.make(O, H, nvec)
+        return lib.ppo_debug_update_tc_variant(C.byref(d), int(masked))
+    assert variant(4, 64, [2]) == 22 and variant(2, 64, [3]) == 23
+    assert variant(2, 64, [3], masked=True) == 20          # masked single head: generic path, still two streams
+    assert variant(4, 64, [3, 3, 3, 3, 3, 2, 2, 2], masked=True) == 10
+    assert variant(4, 256, [2]) == -1 and variant(4, 64, [40]) == -1
