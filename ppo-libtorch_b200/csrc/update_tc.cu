@@ -19,6 +19,10 @@
 //                                                                         G3 : dW2 += A2^T A1 ; d[.|b2] += A2^T XE (doneW)
 //   P4  dZ1 = Z (1 - h1^2)                  -> A2                         G0': Z = XE' P1h^T of the NEXT tile   (doneZ)
 //                                                                         G4 : d[W1|b1] += A2^T XE              (doneW)
+// Head layouts other than one unmasked head of 2 / 3 logits (KT = 0, up to 21 logits over any number of heads, optional
+// mask) also run the actor's output layer on the tensor core: G7 : logits = A2 W3^T between the two halves of P2 (W3 as
+// 16-bit hi + lo, so that only h2 carries a 16-bit rounding) and G6 : Z = DO W3 issued with G5, which P3 reads instead
+// of forming dOut W3 row by row.
 // Compute threads only stage operands and arrive on ready[c]; warp c of the issue warpgroup replays the fixed stage
 // order for compute warpgroup c and issues the MMAs (every tcgen05.mma of these shapes holds the issuing warp ~58
 // cycles).  Completions come back through two mbarriers per compute warpgroup: "doneZ" (an accumulator to read) and
