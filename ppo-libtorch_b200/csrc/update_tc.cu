@@ -61,6 +61,11 @@ struct TcLayout {   // byte offsets into the 1024-aligned dynamic shared memory
     int w3k;         // W3 as two 16-bit K-major swizzled tiles [n7 units][64] (hi, lo at + n7 * 128): B of the logits MMA (G7)
     int w3t;         // W3^T [64 hidden][16 kq units] 16-bit K-major narrow chunks: B of the dh2 MMA (G6)
     int n7, kq;      // N of G7 (K rounded up to 16), K-steps of G6 (n3a rounded up to 16, / 16)
+    // single-head path (KT > 0): one 128B-swizzled [128 rows][64] tile whose logical 16-byte chunk c = 4 g + 2 net + parity
+    // holds that chain's {obs, 1, 0..} (the hi halves of XE).  Addressed as the second 64-column group of the B operand of
+    // dW2 += dZ2^T h1 (leading-dimension offset of the descriptor), it turns that MMA into dZ2^T [h1 | XE] with N = 72:
+    // the separate d[.|b2] += dZ2^T XE series (8 MMAs that re-read the 16 KB dZ2 tile for 64 column sums) disappears.
+    int xt;          // -1: not present (generic layouts have no room for it)
 };
 // tensor-memory columns of the logits accumulator of stream g (generic path), behind the gradient accumulators
 __host__ __device__ constexpr int tc_lgcol(int np, int g, int n3a) { return np * 128 + np * (80 + n3a) + g * 32; }
@@ -92,7 +97,11 @@ __host__ __device__ constexpr TcLayout tc_layout(int K, int np, bool gen = false
     o = (o + 127) & ~127;
     L.p1h_0 = o; o += 4 * TC_H * 16;
     L.p1h_1 = o; o += 4 * TC_H * 16;
-    L.w3k = 0; L.w3t = 0;
+    L.w3k = 0; L.w3t = 0; L.xt = -1;
+    if (!gen) {
+        o = (o + 1023) & ~1023;
+        L.xt = o; o += ACT_BYTES;
+    }
     if (gen) {
         o = (o + 1023) & ~1023;
         L.w3k = o; o += 2 * L.n7 * 128;          // hi tile, lo tile at + n7 * 128 (2 or 4 KB: swizzle-atom aligned)
@@ -199,14 +208,23 @@ __device__ __forceinline__ void issue_stage(WgIssue& w, const TcLayout& L, int p
         const uint64_t dw = act_desc_mnmajor(W2, 0), dh = act_desc_mnmajor(A1, 0);
         const uint64_t dx = narrow_desc_mnmajor(wb + L.xe(par), TC_ROWS, 0);
         const uint32_t acc0 = fresh & 1u ? 0u : 1u;
+        // B = [h1 | XE]: the second 64-column group of the MN-major operand lies LBO bytes behind the first (layout: xt)
+        constexpr uint32_t id_dw72 = idesc_f16(FMT, 64, 72, 1, 1);
+        const uint32_t xt_chunk = sb + (uint32_t)L.xt + 16u * (uint32_t)(4 * g + 2 * net + par);
+        const uint64_t dh72 = smem_desc(A1, xt_chunk - A1, 1024, LAYOUT_SW128);
         if (lead) {
 #pragma unroll
             for (int ks = 0; ks < 4; ks++) mma_f16(Z, dak + 2u * ks, dw + 128u * ks, id_dx, ks > 0);
             mma_commit(doneZ);
+            if (!GEN) {
 #pragma unroll
-            for (int ks = 0; ks < 8; ks++) {
-                mma_f16(tmem + c.w2, dam + 128u * ks, dh + 128u * ks, id_dw, ks > 0 ? 1u : acc0);
-                mma_f16(tmem + c.xe2, dam + 128u * ks, dx + 16u * ks, id_n8, ks > 0 ? 1u : acc0);
+                for (int ks = 0; ks < 8; ks++) mma_f16(tmem + c.w2, dam + 128u * ks, dh72 + 128u * ks, id_dw72, ks > 0 ? 1u : acc0);
+            } else {
+#pragma unroll
+                for (int ks = 0; ks < 8; ks++) {
+                    mma_f16(tmem + c.w2, dam + 128u * ks, dh + 128u * ks, id_dw, ks > 0 ? 1u : acc0);
+                    mma_f16(tmem + c.xe2, dam + 128u * ks, dx + 16u * ks, id_n8, ks > 0 ? 1u : acc0);
+                }
             }
             mma_commit(doneW);
         }
@@ -387,6 +405,7 @@ __device__ __forceinline__ void tc_compute_wg(const UpdArgs& a, const TcLayout& 
         }
         store8<FMT>(wg + L.xe(par_) + wt * 16, xe);
         store8<FMT>(wg + L.xe(par_) + TC_ROWS * 16 + wt * 16, lo);
+        if (FAST) store8<FMT>(sm + L.xt + act_chunk_off(wt, 4 * g + 2 * NET + par_), xe);   // the copy dW2's MMA reads (layout: xt)
     };
     TcRowIn cur = gather(tile0);
     int tiles_done = 0;
@@ -801,7 +820,7 @@ __global__ void __launch_bounds__((2 * NP + 1) * 128, 1) update_tc_kernel(const 
                 mbar_wait(ready, pr); pr ^= 1u;
                 issue_stage<FMT, NP, 1, KT == 0>(D, L, par, doneZ, doneW);
                 mbar_wait(ready, pr); pr ^= 1u;
-                issue_stage<FMT, NP, 2>(D, L, par, doneZ, doneW);
+                issue_stage<FMT, NP, 2, KT == 0>(D, L, par, doneZ, doneW);
                 mbar_wait(ready, pr); pr ^= 1u;
                 issue_stage<FMT, NP, 3>(D, L, par, doneZ, doneW, has_next);
             }
